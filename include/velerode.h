@@ -1,0 +1,138 @@
+/* velerode.h — C ABI of libvelerode.so: the B200 (sm_100a) implementation of Veloren's
+ * world-map erosion pass.
+ *
+ * The reference has no FFI boundary for this path; the boundary it offers is the Rust function
+ *   pub fn do_erosion(map_size_lg, _max_uplift, n_steps, seed, rock_strength_nz, oldh, oldb,
+ *                     is_ocean, uplift, n, theta, kf, kd, g, epsilon_0, alpha, height_scale,
+ *                     k_d_scale, k_da_scale, threadpool, report_progress) -> (Box<[f64]>, Box<[f64]>)
+ * at world/src/sim/erosion.rs:2524-2547, called from WorldSim::generate
+ * (world/src/sim/mod.rs:1370, 1399, 1449).  A Rust shim with that exact signature evaluates
+ * each closure once into a flat array (what erosion.rs:2549-2609 already does) and calls the
+ * entry points below; INTEGRATION.md shows the shim.  All pointers are HOST pointers unless a
+ * comment says otherwise; the library copies what it needs and never keeps caller memory.
+ * Every function returns 0 on success or a negative ve_status; ve_last_error() gives text.
+ * There is no CPU fallback: without a CUDA device ve_create fails with VE_ERR_CUDA.
+ */
+#ifndef VELERODE_H
+#define VELERODE_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ve_ctx ve_ctx;
+
+typedef enum {
+    VE_OK = 0,
+    VE_ERR_CUDA = -1,              /* any CUDA runtime failure (text in ve_last_error) */
+    VE_ERR_INVALID = -2,           /* bad argument / call order */
+    VE_ERR_DISCONNECTED_LAKE = -3, /* panic!("Disconnected lake!") erosion.rs:1251, 1617 */
+    VE_ERR_TRIDAG_SINGULAR = -4,   /* assert_ne!(bet, 0.0) diffusion.rs:423, 445 */
+    VE_ERR_STACK_INCOMPLETE = -5,  /* assert_eq!(stack.len(), nn) erosion.rs:2510; newh 1903/2291 */
+    VE_ERR_LAKE_GRAPH = -6,        /* assert!/assert_ne! inside get_lakes (2089, 2174, 2209, 2262) */
+    VE_ERR_TOO_LARGE = -7
+} ve_status;
+
+/* Per-cell inputs, N = 2^x_lg * 2^y_lg entries each, index = y * nx + x
+ * (common/src/terrain/mod.rs:407-418).  Exactly the arrays do_erosion materialises at
+ * erosion.rs:2549-2609 plus height_scale(n[i]) (erosion.rs:848-850). */
+typedef struct {
+    const float* oldh;              /* oldh(posi)                      erosion.rs:2549 */
+    const float* oldb;              /* oldb(posi)                      erosion.rs:2555 */
+    const uint8_t* is_ocean;        /* is_ocean(posi)                  erosion.rs:818  */
+    const float* uplift;            /* uplift(posi) as f32             erosion.rs:2605 */
+    const float* n;                 /* n(posi)                         erosion.rs:2561 */
+    const float* m;                 /* theta(posi) * n(posi), in f32   erosion.rs:2568 */
+    const float* g;                 /*                                 erosion.rs:2586 */
+    const float* epsilon_0;         /*                                 erosion.rs:2591 */
+    const float* alpha;             /*                                 erosion.rs:2596 */
+    const double* kf;               /*                                 erosion.rs:2574 */
+    const double* kd;               /*                                 erosion.rs:2580 */
+    const double* height_scale_cell;/* height_scale(n(posi))           erosion.rs:848  */
+} ve_inputs;
+
+/* Scalars the Rust host evaluates with its own libm so they carry the host's rounding. */
+typedef struct {
+    double k_d_scale;          /* do_erosion argument; kdsed = 1.5e-2/4*k_d_scale (2635) */
+    double k_da;               /* 2.5 * k_da_scale(0.2)                  erosion.rs:745-750 */
+    double chunk_area_pow_q;   /* (32*32 as f64).powf(0.2)               erosion.rs:926 */
+    double min_max_angle;      /* tan(15 deg)                            erosion.rs:556 */
+    double max_max_angle;      /* tan(60 deg)                            erosion.rs:557 */
+    double mid_slope;          /* tan(30 deg)                            erosion.rs:863 */
+    double mountain_scale;     /* CONFIG.mountain_scale = 2048           world/src/config.rs:62 */
+} ve_params;
+
+/* rock_strength_nz as tables: noise 0.9.0 Fbm<Perlin> (world/src/sim/mod.rs:828-837).
+ * perm holds `octaves` permutation tables of 256 bytes (Perlin::new(seed + i)). */
+typedef struct {
+    uint32_t octaves;
+    double frequency, lacunarity, persistence, scale_factor;
+    const uint8_t* perm;
+} ve_noise_fbm_perlin3;
+
+/* Arrays of the last step that ve_get_array can download (test hook). */
+typedef enum {
+    VE_H = 0, VE_B, VE_WH, VE_DH, VE_INDIRECTION, VE_NEWH, VE_MREC, VE_MSTACK, VE_MWREC, VE_AREA,
+    VE_MAX_SLOPE, VE_KFS, VE_KDF, VE_H_SPL, VE_LAKE_SILT, VE_LAKE_SILL, VE_LAKE_WATER_VOLUME,
+    VE_KD_EFF, VE_DH0, VE_WH_MREC, VE_B_SPL, VE_H_PRE_DIFF, VE_ARRAY_COUNT
+} ve_array;
+
+/* Scalars of the last step (ve_get_scalar). */
+typedef enum {
+    VE_S_N_GS = 0, VE_S_ERR, VE_S_MAXH, VE_S_BOUNDARY_LEN, VE_S_N_LAKES, VE_S_MAX_UPLIFT, VE_S_MAX_G,
+    VE_S_N_UNDERWATER
+} ve_scalar;
+
+void ve_default_params(ve_params* p);
+/* One context per map and per calling thread (batch_generate runs several worlds on
+ * independent threads, world/examples/batch_generate.rs:287-352).  device_ids/n_devices:
+ * GPUs to use; round 1 uses device_ids[0] (NULL -> current device). */
+int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids, int n_devices);
+void ve_destroy(ve_ctx* ctx);
+const char* ve_last_error(ve_ctx* ctx);
+
+int ve_set_params(ve_ctx* ctx, const ve_params* p);
+int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz);
+/* Uploads the inputs and initialises h = oldh as f64, b = oldb as f64, wh = 0
+ * (erosion.rs:2549-2559, 2601); computes max_uplift and max_g (2617-2626). */
+int ve_set_inputs(ve_ctx* ctx, const ve_inputs* in);
+/* Replace the evolving state (any pointer may be NULL to keep it). */
+int ve_set_state(ve_ctx* ctx, const double* h, const double* b, const double* wh);
+
+/* do_erosion's loop (erosion.rs:2645-2681): n_steps erode() calls; `progress` is called on
+ * the calling thread with the percentage at the reference's cadence (2648-2651).  out_h/out_b:
+ * caller-owned, N doubles each. */
+int ve_run(ve_ctx* ctx, uint32_t n_steps, void (*progress)(void* user, double pct), void* user,
+           double* out_h, double* out_b);
+/* One erode() (erosion.rs:699), state stays on the device. */
+int ve_step(ve_ctx* ctx);
+/* Device-resident variant used by the benchmark: n_steps erode() calls, no host copies. */
+int ve_run_device(ve_ctx* ctx, uint32_t n_steps);
+int ve_get_array(ve_ctx* ctx, int which, void* dst);
+size_t ve_array_bytes(ve_ctx* ctx, int which);
+double ve_get_scalar(ve_ctx* ctx, int which);
+/* number of kernels launched by this context so far, and seconds spent per stage of the last
+ * step (names via ve_timer_name) when ve_set_timing(ctx, 1) is on (adds synchronisations). */
+uint64_t ve_launch_count(ve_ctx* ctx);
+int ve_set_timing(ve_ctx* ctx, int on);
+int ve_get_timers(ve_ctx* ctx, double* dst, int cap);
+const char* ve_timer_name(int i);
+
+/* Post-erosion hydrology calls of WorldSim::generate (world/src/sim/mod.rs:1474-1550): the
+ * same kernels, on caller-supplied host arrays.  The context only provides device scratch. */
+int ve_downhill(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, int32_t* dh);  /* util.rs:251 */
+int ve_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh /*in-out*/, int32_t* indirection,
+                 uint32_t* newh, double* maxh, uint64_t* boundary_len);                /* erosion.rs:1825 */
+int ve_get_multi_rec(ve_ctx* ctx, const double* h, const int32_t* dh, const uint32_t* newh,
+                     double* wh /*in-out*/, uint8_t* mrec, uint32_t* mstack, double* mwrec); /* 2332 */
+int ve_get_multi_drainage(ve_ctx* ctx, const uint32_t* mstack, const uint8_t* mrec,
+                          const double* mwrec, double* area);                          /* erosion.rs:62 */
+int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double* out); /* erosion.rs:1738 */
+int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux); /* erosion.rs:29-58 */
+int ve_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd);       /* diffusion.rs:41 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

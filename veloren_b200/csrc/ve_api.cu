@@ -1,0 +1,448 @@
+// ve_api.cu — C ABI of libvelerode.so (include/velerode.h) and the erode() step driver.
+#include "ve_internal.cuh"
+#include <math.h>
+#include <string.h>
+#include <chrono>
+
+static const char* TIMER_NAMES[VT_COUNT] = {"downhill", "get_lakes", "wh_fill", "mrec", "stack", "area", "max_slope",
+                                            "k_factors", "gs_down", "gs_up", "gs_lwv", "basement", "thermal",
+                                            "diffusion", "total"};
+
+int ve_scratch(ve_ctx* ctx, int i, size_t bytes, void** out) {
+    if (bytes < 256) bytes = 256;
+    if (ctx->scratch_bytes[i] < bytes) {
+        if (ctx->scratch[i]) { VE_CUDA(cudaStreamSynchronize(ctx->stream)); VE_CUDA(cudaFree(ctx->scratch[i])); ctx->scratch[i] = nullptr; ctx->scratch_bytes[i] = 0; }
+        size_t want = bytes + bytes / 8;
+        VE_CUDA(cudaMalloc(&ctx->scratch[i], want));
+        ctx->scratch_bytes[i] = want;
+    }
+    *out = ctx->scratch[i];
+    return VE_OK;
+}
+int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out) {
+    if (bytes < 256) bytes = 256;
+    if (ctx->cub_tmp_bytes < bytes) {
+        if (ctx->cub_tmp) { VE_CUDA(cudaStreamSynchronize(ctx->stream)); VE_CUDA(cudaFree(ctx->cub_tmp)); ctx->cub_tmp = nullptr; ctx->cub_tmp_bytes = 0; }
+        VE_CUDA(cudaMalloc(&ctx->cub_tmp, bytes * 2));
+        ctx->cub_tmp_bytes = bytes * 2;
+    }
+    *out = ctx->cub_tmp;
+    return VE_OK;
+}
+int ve_check_abort(ve_ctx* ctx) {
+    uint32_t a = 0;
+    VE_CUDA(cudaMemcpyAsync(&a, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->df_pending = 0;
+    if (a) {
+        cudaMemsetAsync(ctx->abort_word, 0, 4, ctx->stream);
+        ctx->err = "dataflow sweep stalled: order is not topological (stack/newh incomplete)";
+        return VE_ERR_STACK_INCOMPLETE;
+    }
+    return VE_OK;
+}
+
+template <class T> static int dev_alloc(ve_ctx* ctx, T** p, size_t count) {
+    VE_CUDA(cudaMalloc((void**)p, count * sizeof(T)));
+    VE_CUDA(cudaMemset(*p, 0, count * sizeof(T)));
+    return VE_OK;
+}
+
+__global__ void k_f32_to_f64(uint32_t n, const float* __restrict__ a, double* __restrict__ o) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = (double)a[i];
+}
+
+// lake_silt / lake_sill are kept per grid cell on the device; the reference indexes them by
+// stack position, so the download permutes them (out[stackpos[i]] = a[i]) for comparison.
+template <class T> __global__ void k_to_stack_index(uint32_t n, const T* __restrict__ a, const uint32_t* __restrict__ stackpos, T* __restrict__ o) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[stackpos[i]] = a[i];
+}
+
+extern "C" {
+
+void ve_default_params(ve_params* p) {
+    const double PI = 3.14159265358979323846;
+    p->k_d_scale = 0.5;
+    p->k_da = 2.5 * pow(0.5, -2.0 * 0.2);
+    p->chunk_area_pow_q = pow(1024.0, 0.2);
+    p->min_max_angle = tan(15.0 / 360.0 * 2.0 * PI);
+    p->max_max_angle = tan(60.0 / 360.0 * 2.0 * PI);
+    p->mid_slope = tan(30.0 / 360.0 * 2.0 * PI);
+    p->mountain_scale = 2048.0;
+}
+
+static int create_impl(ve_ctx* ctx, uint32_t x_lg, uint32_t y_lg, const int* device_ids, int n_devices) {
+    int ndev = 0;
+    VE_CUDA(cudaGetDeviceCount(&ndev));
+    if (ndev < 1) { ctx->err = "no CUDA device"; return VE_ERR_CUDA; }
+    int dev = 0;
+    if (device_ids && n_devices > 0) dev = device_ids[0];
+    else VE_CUDA(cudaGetDevice(&dev));
+    VE_CUDA(cudaSetDevice(dev));
+    ctx->device = dev;
+    cudaDeviceProp prop;
+    VE_CUDA(cudaGetDeviceProperties(&prop, dev));
+    ctx->sm_count = prop.multiProcessorCount;
+    int coop = 0;
+    VE_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    if (!coop) { ctx->err = "device lacks cooperative launch"; return VE_ERR_CUDA; }
+    VE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    Geom& g = ctx->g;
+    g.xlg = x_lg; g.ylg = y_lg; g.nx = 1 << x_lg; g.ny = 1 << y_lg; g.n = (uint32_t)g.nx * (uint32_t)g.ny;
+    size_t n = g.n;
+    VE_TRY(dev_alloc(ctx, &ctx->uplift, n)); VE_TRY(dev_alloc(ctx, &ctx->nf, n)); VE_TRY(dev_alloc(ctx, &ctx->mf, n));
+    VE_TRY(dev_alloc(ctx, &ctx->gf, n)); VE_TRY(dev_alloc(ctx, &ctx->eps0, n)); VE_TRY(dev_alloc(ctx, &ctx->alpha, n));
+    VE_TRY(dev_alloc(ctx, &ctx->kf, n)); VE_TRY(dev_alloc(ctx, &ctx->kd, n)); VE_TRY(dev_alloc(ctx, &ctx->hscale, n));
+    VE_TRY(dev_alloc(ctx, &ctx->ocean, n));
+    VE_TRY(dev_alloc(ctx, &ctx->h, n)); VE_TRY(dev_alloc(ctx, &ctx->b, n)); VE_TRY(dev_alloc(ctx, &ctx->wh, n));
+    VE_TRY(dev_alloc(ctx, &ctx->dh, n)); VE_TRY(dev_alloc(ctx, &ctx->dh0, n)); VE_TRY(dev_alloc(ctx, &ctx->indirection, n));
+    VE_TRY(dev_alloc(ctx, &ctx->newh, n)); VE_TRY(dev_alloc(ctx, &ctx->mstack, n)); VE_TRY(dev_alloc(ctx, &ctx->stackpos, n));
+    VE_TRY(dev_alloc(ctx, &ctx->mrec, n)); VE_TRY(dev_alloc(ctx, &ctx->ndon, n));
+    VE_TRY(dev_alloc(ctx, &ctx->mwrec, n * 8));
+    VE_TRY(dev_alloc(ctx, &ctx->area, n)); VE_TRY(dev_alloc(ctx, &ctx->max_slope, n)); VE_TRY(dev_alloc(ctx, &ctx->kd_eff, n));
+    VE_TRY(dev_alloc(ctx, &ctx->h_t, n)); VE_TRY(dev_alloc(ctx, &ctx->h_new, n)); VE_TRY(dev_alloc(ctx, &ctx->deltah, n));
+    VE_TRY(dev_alloc(ctx, &ctx->elev, n)); VE_TRY(dev_alloc(ctx, &ctx->h_p, n)); VE_TRY(dev_alloc(ctx, &ctx->lake_silt, n));
+    VE_TRY(dev_alloc(ctx, &ctx->lwv, n)); VE_TRY(dev_alloc(ctx, &ctx->wh_prev, n)); VE_TRY(dev_alloc(ctx, &ctx->h_spl, n));
+    VE_TRY(dev_alloc(ctx, &ctx->b_spl, n)); VE_TRY(dev_alloc(ctx, &ctx->wh_mrec, n)); VE_TRY(dev_alloc(ctx, &ctx->h_pre_diff, n));
+    VE_TRY(dev_alloc(ctx, &ctx->kfs, n * 8)); VE_TRY(dev_alloc(ctx, &ctx->kdf, n * 8));
+    VE_TRY(dev_alloc(ctx, &ctx->sill_cur, n)); VE_TRY(dev_alloc(ctx, &ctx->sill_prev, n));
+    VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
+    VE_TRY(dev_alloc(ctx, &ctx->f_parent, n)); VE_TRY(dev_alloc(ctx, &ctx->f_jump, n)); VE_TRY(dev_alloc(ctx, &ctx->f_depth, n));
+    VE_TRY(dev_alloc(ctx, &ctx->f_root, n));
+    VE_TRY(dev_alloc(ctx, &ctx->abort_word, 64));
+    VE_TRY(dev_alloc(ctx, &ctx->d_scalars, 64));
+    VE_CUDA(cudaMallocHost((void**)&ctx->h_scalars, 64 * sizeof(double)));
+    return VE_OK;
+}
+
+int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids, int n_devices) {
+    if (!out || x_lg < 2 || y_lg < 2 || x_lg + y_lg > 28) return VE_ERR_INVALID;
+    ve_ctx* ctx = new ve_ctx();
+    memset((void*)&ctx->g, 0, sizeof(Geom));
+    ctx->stream = nullptr; ctx->timing = false; ctx->launches = 0; ctx->epoch = 0; ctx->df_pending = 0;
+    ctx->max_uplift = 0; ctx->max_g = 0; ctx->n_gs = 0; ctx->gs_err = 0; ctx->maxh = 0; ctx->boundary_len = 0;
+    ctx->n_lakes = 0; ctx->n_underwater = 0; ctx->cub_tmp = nullptr; ctx->cub_tmp_bytes = 0;
+    memset(ctx->scratch, 0, sizeof(ctx->scratch)); memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
+    memset(ctx->timers, 0, sizeof(ctx->timers));
+    memset(&ctx->nz, 0, sizeof(ctx->nz));
+    ve_default_params(&ctx->P);
+    *out = ctx;
+    return create_impl(ctx, x_lg, y_lg, device_ids, n_devices);
+}
+
+void ve_destroy(ve_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    void* ptrs[] = {ctx->uplift, ctx->nf, ctx->mf, ctx->gf, ctx->eps0, ctx->alpha, ctx->kf, ctx->kd, ctx->hscale, ctx->ocean,
+                    ctx->h, ctx->b, ctx->wh, ctx->dh, ctx->dh0, ctx->indirection, ctx->newh, ctx->mstack, ctx->stackpos,
+                    ctx->mrec, ctx->ndon, ctx->mwrec, ctx->area, ctx->max_slope, ctx->kd_eff, ctx->h_t, ctx->h_new,
+                    ctx->deltah, ctx->elev, ctx->h_p, ctx->lake_silt, ctx->lwv, ctx->wh_prev, ctx->h_spl, ctx->b_spl,
+                    ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td,
+                    ctx->don_order, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
+                    ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* ve_last_error(ve_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int ve_set_params(ve_ctx* ctx, const ve_params* p) {
+    if (!ctx || !p) return VE_ERR_INVALID;
+    ctx->P = *p;
+    return VE_OK;
+}
+
+int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz) {
+    if (!ctx || !nz || !nz->perm || nz->octaves == 0 || nz->octaves > 32) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->nz.perm) { cudaFree(ctx->nz.perm); ctx->nz.perm = nullptr; }
+    VE_CUDA(cudaMalloc((void**)&ctx->nz.perm, (size_t)nz->octaves * 256));
+    VE_CUDA(cudaMemcpy(ctx->nz.perm, nz->perm, (size_t)nz->octaves * 256, cudaMemcpyHostToDevice));
+    ctx->nz.octaves = nz->octaves; ctx->nz.frequency = nz->frequency; ctx->nz.lacunarity = nz->lacunarity;
+    ctx->nz.persistence = nz->persistence; ctx->nz.scale_factor = nz->scale_factor;
+    return VE_OK;
+}
+
+int ve_set_inputs(ve_ctx* ctx, const ve_inputs* in) {
+    if (!ctx || !in) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    cudaStream_t st = ctx->stream;
+    float* tmp;
+    VE_TRY(ve_scratch(ctx, 0, n * 4, (void**)&tmp));
+    // h = oldh as f64, b = oldb as f64, wh = 0 (erosion.rs:2549-2559, 2601)
+    VE_CUDA(cudaMemcpyAsync(tmp, in->oldh, n * 4, cudaMemcpyHostToDevice, st));
+    k_f32_to_f64<<<ve_blocks(n, 256), 256, 0, st>>>((uint32_t)n, tmp, ctx->h); VE_LAUNCH_CHECK();
+    VE_CUDA(cudaStreamSynchronize(st));
+    VE_CUDA(cudaMemcpyAsync(tmp, in->oldb, n * 4, cudaMemcpyHostToDevice, st));
+    k_f32_to_f64<<<ve_blocks(n, 256), 256, 0, st>>>((uint32_t)n, tmp, ctx->b); VE_LAUNCH_CHECK();
+    VE_CUDA(cudaMemsetAsync(ctx->wh, 0, n * 8, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->ocean, in->is_ocean, n, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->uplift, in->uplift, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->nf, in->n, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->mf, in->m, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->gf, in->g, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->eps0, in->epsilon_0, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->alpha, in->alpha, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->kf, in->kf, n * 8, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->kd, in->kd, n * 8, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(ctx->hscale, in->height_scale_cell, n * 8, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaStreamSynchronize(st));
+    // max_uplift / max_g (erosion.rs:2617-2626): scalar reductions over the host arrays the shim already holds
+    float mu = in->uplift[0], mg = in->g[0];
+    for (size_t i = 1; i < n; ++i) { if (in->uplift[i] > mu) mu = in->uplift[i]; if (in->g[i] > mg) mg = in->g[i]; }
+    ctx->max_uplift = mu; ctx->max_g = mg;
+    return VE_OK;
+}
+
+int ve_set_state(ve_ctx* ctx, const double* h, const double* b, const double* wh) {
+    if (!ctx) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t nb = (size_t)ctx->g.n * 8;
+    if (h) VE_CUDA(cudaMemcpyAsync(ctx->h, h, nb, cudaMemcpyHostToDevice, ctx->stream));
+    if (b) VE_CUDA(cudaMemcpyAsync(ctx->b, b, nb, cudaMemcpyHostToDevice, ctx->stream));
+    if (wh) VE_CUDA(cudaMemcpyAsync(ctx->wh, wh, nb, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+struct StageTimer {
+    ve_ctx* ctx; int id; std::chrono::steady_clock::time_point t0;
+    StageTimer(ve_ctx* c, int i) : ctx(c), id(i) { if (ctx->timing) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); } }
+    void stop() {
+        if (ctx->timing) {
+            cudaStreamSynchronize(ctx->stream);
+            ctx->timers[id] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        }
+    }
+};
+
+// erode(): erosion.rs:699-1731
+int ve_step(ve_ctx* ctx) {
+    if (!ctx) return VE_ERR_INVALID;
+    if (!ctx->nz.perm) { ctx->err = "ve_set_noise not called"; return VE_ERR_INVALID; }
+    VE_CUDA(cudaSetDevice(ctx->device));
+    const size_t nb8 = (size_t)ctx->g.n * 8;
+    memset(ctx->timers, 0, sizeof(ctx->timers));
+    auto t_all = std::chrono::steady_clock::now();
+    const double dt = (double)ctx->max_uplift / 1e-3;
+    { StageTimer t(ctx, VT_DOWNHILL); VE_TRY(ve_k_downhill(ctx, ctx->h, ctx->ocean, 1, ctx->dh)); t.stop(); }          // 815-819
+    { StageTimer t(ctx, VT_LAKES); VE_TRY(ve_l_get_lakes(ctx, ctx->h, ctx->dh, ctx->indirection, ctx->newh)); t.stop(); } // 821-822
+    { StageTimer t(ctx, VT_WHFILL); VE_TRY(ve_g_wh_fill(ctx)); VE_TRY(ve_check_abort(ctx)); t.stop(); }                 // 2383-2400
+    { StageTimer t(ctx, VT_MREC); VE_TRY(ve_k_mrec(ctx));                                                               // 2407-2479
+      VE_CUDA(cudaMemcpyAsync(ctx->wh_mrec, ctx->wh, nb8, cudaMemcpyDeviceToDevice, ctx->stream)); t.stop(); }
+    { StageTimer t(ctx, VT_STACK); VE_TRY(ve_g_stack(ctx)); VE_TRY(ve_check_abort(ctx)); t.stop(); }                    // 2483-2511
+    { StageTimer t(ctx, VT_AREA); VE_TRY(ve_g_area(ctx)); t.stop(); }                                                   // 841
+    { StageTimer t(ctx, VT_SLOPE); VE_TRY(ve_k_max_slope(ctx)); t.stop(); }                                             // 845-856
+    { StageTimer t(ctx, VT_KFACT); VE_TRY(ve_k_kfactors(ctx)); t.stop(); }                                              // 870-1006
+    VE_TRY(ve_g_spl_solve(ctx));                                                                                         // 1076-1475
+    VE_TRY(ve_check_abort(ctx));
+    { StageTimer t(ctx, VT_BASEMENT); VE_TRY(ve_k_basement(ctx)); t.stop(); }                                           // 1483-1556
+    { StageTimer t(ctx, VT_THERMAL); VE_TRY(ve_g_thermal_wh(ctx)); VE_TRY(ve_k_thermal_kd(ctx));                        // 1597-1696
+      VE_CUDA(cudaMemcpyAsync(ctx->h_pre_diff, ctx->h, nb8, cudaMemcpyDeviceToDevice, ctx->stream)); t.stop(); }
+    { StageTimer t(ctx, VT_DIFFUSION); VE_TRY(ve_k_diffusion(ctx, dt, ctx->h, ctx->b, ctx->kd_eff)); t.stop(); }        // 1717-1728
+    VE_TRY(ve_check_abort(ctx));
+    ctx->timers[VT_TOTAL] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_all).count();
+    return VE_OK;
+}
+
+int ve_run_device(ve_ctx* ctx, uint32_t n_steps) {
+    for (uint32_t i = 0; i < n_steps; ++i) VE_TRY(ve_step(ctx));
+    return VE_OK;
+}
+
+int ve_run(ve_ctx* ctx, uint32_t n_steps, void (*progress)(void* user, double pct), void* user, double* out_h, double* out_b) {
+    if (!ctx) return VE_ERR_INVALID;
+    for (uint32_t i = 0; i < n_steps; ++i) {
+        uint32_t every = n_steps / 100 > 1 ? n_steps / 100 : 1;       // erosion.rs:2649
+        if (progress && i % every == 0) progress(user, ((double)i / (double)n_steps) * 100.0);
+        VE_TRY(ve_step(ctx));
+    }
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t nb = (size_t)ctx->g.n * 8;
+    if (out_h) VE_CUDA(cudaMemcpyAsync(out_h, ctx->h, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_b) VE_CUDA(cudaMemcpyAsync(out_b, ctx->b, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+size_t ve_array_bytes(ve_ctx* ctx, int which) {
+    size_t n = ctx->g.n;
+    switch (which) {
+        case VE_H: case VE_B: case VE_WH: case VE_AREA: case VE_MAX_SLOPE: case VE_H_SPL: case VE_LAKE_SILT:
+        case VE_LAKE_WATER_VOLUME: case VE_KD_EFF: case VE_WH_MREC: case VE_B_SPL: case VE_H_PRE_DIFF: return n * 8;
+        case VE_MWREC: return n * 64;
+        case VE_DH: case VE_DH0: case VE_INDIRECTION: case VE_NEWH: case VE_MSTACK: case VE_LAKE_SILL: return n * 4;
+        case VE_MREC: return n;
+        case VE_KFS: case VE_KDF: return n * 32;
+    }
+    return 0;
+}
+
+int ve_get_array(ve_ctx* ctx, int which, void* dst) {
+    if (!ctx || !dst) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    const void* src = nullptr;
+    uint32_t n = ctx->g.n;
+    switch (which) {
+        case VE_H: src = ctx->h; break;                  case VE_B: src = ctx->b; break;
+        case VE_WH: src = ctx->wh; break;                case VE_DH: src = ctx->dh; break;
+        case VE_INDIRECTION: src = ctx->indirection; break; case VE_NEWH: src = ctx->newh; break;
+        case VE_MREC: src = ctx->mrec; break;            case VE_MSTACK: src = ctx->mstack; break;
+        case VE_MWREC: src = ctx->mwrec; break;          case VE_AREA: src = ctx->area; break;
+        case VE_MAX_SLOPE: src = ctx->max_slope; break;  case VE_KFS: src = ctx->kfs; break;
+        case VE_KDF: src = ctx->kdf; break;              case VE_H_SPL: src = ctx->h_spl; break;
+        case VE_LAKE_WATER_VOLUME: src = ctx->lwv; break; case VE_KD_EFF: src = ctx->kd_eff; break;
+        case VE_DH0: src = ctx->dh0; break;              case VE_WH_MREC: src = ctx->wh_mrec; break;
+        case VE_B_SPL: src = ctx->b_spl; break;          case VE_H_PRE_DIFF: src = ctx->h_pre_diff; break;
+        case VE_LAKE_SILT: {
+            double* t; VE_TRY(ve_scratch(ctx, 0, (size_t)n * 8, (void**)&t));
+            k_to_stack_index<double><<<ve_blocks(n, 256), 256, 0, ctx->stream>>>(n, ctx->lake_silt, ctx->stackpos, t); VE_LAUNCH_CHECK();
+            src = t; break;
+        }
+        case VE_LAKE_SILL: {
+            int32_t* t; VE_TRY(ve_scratch(ctx, 0, (size_t)n * 4, (void**)&t));
+            k_to_stack_index<int32_t><<<ve_blocks(n, 256), 256, 0, ctx->stream>>>(n, ctx->sill_cur, ctx->stackpos, t); VE_LAUNCH_CHECK();
+            src = t; break;
+        }
+        default: return VE_ERR_INVALID;
+    }
+    VE_CUDA(cudaMemcpyAsync(dst, src, ve_array_bytes(ctx, which), cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+double ve_get_scalar(ve_ctx* ctx, int which) {
+    switch (which) {
+        case VE_S_N_GS: return ctx->n_gs;             case VE_S_ERR: return ctx->gs_err;
+        case VE_S_MAXH: return ctx->maxh;             case VE_S_BOUNDARY_LEN: return (double)ctx->boundary_len;
+        case VE_S_N_LAKES: return (double)ctx->n_lakes; case VE_S_MAX_UPLIFT: return (double)ctx->max_uplift;
+        case VE_S_MAX_G: return (double)ctx->max_g;   case VE_S_N_UNDERWATER: return (double)ctx->n_underwater;
+    }
+    return NAN;
+}
+
+uint64_t ve_launch_count(ve_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int ve_set_timing(ve_ctx* ctx, int on) { if (!ctx) return VE_ERR_INVALID; ctx->timing = on != 0; return VE_OK; }
+int ve_get_timers(ve_ctx* ctx, double* dst, int cap) {
+    int k = cap < VT_COUNT ? cap : (int)VT_COUNT;
+    for (int i = 0; i < k; ++i) dst[i] = ctx->timers[i];
+    return VT_COUNT;
+}
+const char* ve_timer_name(int i) { return (i >= 0 && i < VT_COUNT) ? TIMER_NAMES[i] : ""; }
+
+// ---- hydrology entry points (world/src/sim/mod.rs:1474-1550) -----------------------------------
+int ve_downhill(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, int32_t* dh) {
+    if (!ctx || !h || !is_ocean || !dh) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    uint8_t* oc; VE_TRY(ve_scratch(ctx, 0, n, (void**)&oc));
+    VE_CUDA(cudaMemcpyAsync(oc, is_ocean, n, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_k_downhill(ctx, ctx->h_t, oc, 0, ctx->dh));
+    VE_CUDA(cudaMemcpyAsync(dh, ctx->dh, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh, double* maxh, uint64_t* boundary_len) {
+    if (!ctx || !h || !dh || !indirection || !newh) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->dh, dh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_l_get_lakes(ctx, ctx->h_t, ctx->dh, ctx->indirection, ctx->newh));
+    VE_CUDA(cudaMemcpyAsync(dh, ctx->dh, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(indirection, ctx->indirection, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(newh, ctx->newh, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (maxh) *maxh = ctx->maxh;
+    if (boundary_len) *boundary_len = ctx->boundary_len;
+    return VE_OK;
+}
+
+int ve_get_multi_rec(ve_ctx* ctx, const double* h, const int32_t* dh, const uint32_t* newh, double* wh, uint8_t* mrec,
+                     uint32_t* mstack, double* mwrec) {
+    if (!ctx || !h || !dh || !newh || !wh || !mrec || !mstack || !mwrec) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    // uses the context's state slots: h <- h, dh, newh, wh
+    VE_CUDA(cudaMemcpyAsync(ctx->h, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->dh, dh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->newh, newh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->wh, wh, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_wh_fill(ctx)); VE_TRY(ve_check_abort(ctx));
+    VE_TRY(ve_k_mrec(ctx));
+    VE_TRY(ve_g_stack(ctx)); VE_TRY(ve_check_abort(ctx));
+    VE_CUDA(cudaMemcpyAsync(wh, ctx->wh, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(mrec, ctx->mrec, n, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(mstack, ctx->mstack, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(mwrec, ctx->mwrec, n * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_get_multi_drainage(ve_ctx* ctx, const uint32_t* mstack, const uint8_t* mrec, const double* mwrec, double* area) {
+    if (!ctx || !mstack || !mrec || !mwrec || !area) return VE_ERR_INVALID;
+    // The area sweep needs the sweep order and donor lists ve_g_stack derives; rebuilding them from
+    // a caller-supplied mstack would duplicate that stage, so this entry point requires that the
+    // context's last ve_get_multi_rec produced exactly these arrays (the only way the reference
+    // calls it: mod.rs:1480-1496 passes get_multi_rec's outputs straight through).
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    std::vector<uint32_t> chk(n);
+    VE_CUDA(cudaMemcpy(chk.data(), ctx->mstack, n * 4, cudaMemcpyDeviceToHost));
+    if (memcmp(chk.data(), mstack, n * 4) != 0) { ctx->err = "ve_get_multi_drainage: mstack is not the last ve_get_multi_rec result"; return VE_ERR_INVALID; }
+    VE_TRY(ve_g_area(ctx)); VE_TRY(ve_check_abort(ctx));
+    VE_CUDA(cudaMemcpyAsync(area, ctx->area, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double* out) {
+    if (!ctx || !h || !is_ocean || !out) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    uint8_t* oc; VE_TRY(ve_scratch(ctx, 0, n, (void**)&oc));
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(oc, is_ocean, n, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_fill_sinks(ctx, ctx->h_t, oc, ctx->elev));
+    VE_CUDA(cudaMemcpyAsync(out, ctx->elev, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux) {
+    if (!ctx || !newh || !dh || !flux) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    VE_CUDA(cudaMemcpyAsync(ctx->newh, newh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->dh, dh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    float* fl = (float*)ctx->elev;
+    VE_TRY(ve_g_get_drainage(ctx, ctx->newh, ctx->dh, fl)); VE_TRY(ve_check_abort(ctx));
+    VE_CUDA(cudaMemcpyAsync(flux, fl, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd) {
+    if (!ctx || !h || !b || !kd) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->deltah, b, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->elev, kd, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_k_diffusion(ctx, dt, ctx->h_t, ctx->deltah, ctx->elev));
+    VE_CUDA(cudaMemcpyAsync(h, ctx->h_t, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(b, ctx->deltah, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,135 @@
+// ve_internal.cuh — context layout and helpers shared by the libvelerode translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/velerode.h"
+#include "../../include/ve_exact_math.h"
+
+// common/src/terrain/mod.rs:421-430 — slot k <-> 7-k are opposite directions.
+__device__ __constant__ static const int c_ndx[8] = {-1, 0, 1, -1, 1, -1, 0, 1};
+__device__ __constant__ static const int c_ndy[8] = {-1, -1, -1, 0, 0, 1, 1, 1};
+
+struct Geom {
+    uint32_t xlg, ylg;
+    int nx, ny;
+    uint32_t n;
+    __host__ __device__ __forceinline__ int x_of(uint32_t i) const { return (int)(i & ((1u << xlg) - 1u)); }
+    __host__ __device__ __forceinline__ int y_of(uint32_t i) const { return (int)(i >> xlg); }
+    __host__ __device__ __forceinline__ uint32_t idx(int x, int y) const { return ((uint32_t)y << xlg) | (uint32_t)x; }
+    __host__ __device__ __forceinline__ bool inb(int x, int y) const { return x >= 0 && y >= 0 && x < nx && y < ny; }
+};
+
+enum VeTimer {
+    VT_DOWNHILL, VT_LAKES, VT_WHFILL, VT_MREC, VT_STACK, VT_AREA, VT_SLOPE, VT_KFACT, VT_GS_DOWN, VT_GS_UP, VT_GS_LWV,
+    VT_BASEMENT, VT_THERMAL, VT_DIFFUSION, VT_TOTAL, VT_COUNT
+};
+
+struct NoiseDev {
+    uint32_t octaves;
+    double frequency, lacunarity, persistence, scale_factor;
+    uint8_t* perm; // device, octaves*256
+};
+
+// Every per-cell array lives in HBM for the lifetime of the context (DESIGN.md "data layout").
+struct ve_ctx {
+    Geom g;
+    int device;
+    cudaStream_t stream;
+    ve_params P;
+    NoiseDev nz;
+    std::string err;
+    bool timing;
+    uint64_t launches;
+    double timers[VT_COUNT];
+    int sm_count;
+    int df_grid; // resident grid size for the dataflow sweeps
+
+    // inputs
+    float *uplift, *nf, *mf, *gf, *eps0, *alpha;
+    double *kf, *kd, *hscale;
+    uint8_t* ocean;
+    float max_uplift, max_g;
+    // evolving state
+    double *h, *b, *wh;
+    // step intermediates (grid-indexed unless noted)
+    int32_t *dh, *dh0, *indirection;
+    uint32_t *newh, *mstack, *stackpos;
+    uint8_t *mrec, *ndon;
+    double *mwrec;            // [cell][8]
+    double *area, *max_slope, *kd_eff, *h_t, *h_new, *deltah, *elev, *h_p, *lake_silt, *lwv, *wh_prev, *h_spl, *b_spl,
+        *wh_mrec, *h_pre_diff;
+    float *kfs, *kdf;         // [cell][8]
+    int32_t *sill_cur, *sill_prev;
+    uint32_t *order_td;       // topological order, sources first (wh desc, stack position asc)
+    uint32_t *don_order;      // packed donor slots sorted by stack position
+    uint32_t *flags;          // dataflow completion epochs
+    uint32_t epoch;
+    uint32_t* abort_word;     // device word raised by a stalled dataflow sweep
+    int df_pending;
+    // forest scratch (mstack / lakes)
+    uint32_t *f_parent, *f_jump, *f_depth, *f_root;
+    // generic scratch
+    void* scratch[8];
+    size_t scratch_bytes[8];
+    void* cub_tmp; size_t cub_tmp_bytes;
+    double* d_scalars;        // small device scalar block
+    double* h_scalars;        // pinned mirror
+    // last-step scalars
+    int n_gs; double gs_err; double maxh; uint64_t boundary_len; uint32_t n_lakes; uint32_t n_underwater;
+};
+
+#define VE_CUDA(call)                                                                          \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            char buf_[512];                                                                    \
+            snprintf(buf_, sizeof(buf_), "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            ctx->err = buf_;                                                                   \
+            return VE_ERR_CUDA;                                                                \
+        }                                                                                      \
+    } while (0)
+
+#define VE_TRY(call)                   \
+    do {                               \
+        int rc_ = (call);              \
+        if (rc_ != VE_OK) return rc_;  \
+    } while (0)
+
+#define VE_LAUNCH_CHECK()                                   \
+    do {                                                    \
+        ctx->launches++;                                    \
+        VE_CUDA(cudaGetLastError());                        \
+    } while (0)
+
+static inline unsigned ve_blocks(uint64_t n, unsigned bs) { return (unsigned)((n + bs - 1) / bs); }
+
+// scratch buffer i with at least `bytes` bytes (grown on demand; contents undefined)
+int ve_scratch(ve_ctx* ctx, int i, size_t bytes, void** out);
+int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out);
+// synchronise and turn a raised abort word into VE_ERR_STACK_INCOMPLETE
+int ve_check_abort(ve_ctx* ctx);
+
+// ---- stage entry points (one per translation unit) ------------------------------------------
+// ve_stencil.cu
+int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh);
+int ve_k_mrec(ve_ctx* ctx);                 // mrec, ndon, mwrec from ctx->wh
+int ve_k_max_slope(ve_ctx* ctx);
+int ve_k_kfactors(ve_ctx* ctx);
+int ve_k_basement(ve_ctx* ctx);             // scatter is implicit (grid-indexed), basement + lake silt
+int ve_k_thermal_kd(ve_ctx* ctx);
+int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd_eff);
+// ve_graph.cu
+int ve_g_wh_fill(ve_ctx* ctx);              // erosion.rs:2383-2400 along newh
+int ve_g_stack(ve_ctx* ctx);                // exact mstack + stackpos + order_td + don_order
+int ve_g_area(ve_ctx* ctx);
+int ve_g_spl_solve(ve_ctx* ctx);            // Gauss-Seidel loop (erosion.rs:1076-1467)
+int ve_g_thermal_wh(ve_ctx* ctx);           // wh running max along newh (erosion.rs:1620, 1685)
+int ve_g_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux);
+int ve_g_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* ocean, double* out);
+// list ranking over a forest given by successor arcs (shared by stack and lakes)
+int ve_list_rank(ve_ctx* ctx, uint32_t n_arcs, uint32_t* succ /*in, destroyed*/, int32_t* w0, int32_t* w1);
+// ve_lakes.cu
+int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh);

@@ -1,0 +1,597 @@
+// ve_lakes.cu — get_lakes (world/src/sim/erosion.rs:1825-2293) on the GPU.
+//
+// Reference phases and their GPU formulation:
+//  (i)   1865-1902  every dh<0 cell roots a tree; BFS order only matters as a tie-break
+//        -> roots by pointer jumping, (depth, pre-order) keys from an Euler tour + list ranking.
+//  (ii)  1915-2019  one representative pass per adjacent lake pair: min (pass height, BFS
+//        position of the cell in the higher-rooted lake, neighbour slot), strict '<'
+//        -> three passes of atomicMin into a hash table keyed by the lake pair.
+//  (iii)/(iv) 2028-2137  Prim-style growth from the boundary lakes with a heap keyed
+//        (pass height, from, to): order-dependent under ties -> emulated literally by ONE warp
+//        with a 32-ary heap (children scanned by the 32 lanes, min by shuffle).
+//  (v)   2152-2290  per-lake LIFO flood that re-routes flooded cells; lakes are independent
+//        -> one thread per lake; then the final BFS order = stable sort by (block, depth) of the
+//        pre-order of the final forest (Euler tour + list ranking again).
+#include "ve_internal.cuh"
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <algorithm>
+#include <string.h>
+
+__device__ __forceinline__ int l_slot_of(int dx, int dy) { int k = (dy + 1) * 3 + (dx + 1); return k < 4 ? k : k - 1; }
+__device__ __forceinline__ uint64_t l_order_bits(double x) {
+    x = x + 0.0; // -0.0 and +0.0 compare equal in the reference's f64 comparisons
+    uint64_t u = (uint64_t)__double_as_longlong(x);
+    return (u & 0x8000000000000000ULL) ? ~u : (u | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ uint64_t l_hash(uint64_t k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33; return k;
+}
+
+// ---- (i) roots -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_root_init(uint32_t n, const int32_t* __restrict__ dh, uint32_t* __restrict__ root) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { int32_t d = dh[i]; root[i] = d < 0 ? i : (uint32_t)d; }
+}
+__global__ void __launch_bounds__(256) k_root_jump(uint32_t n, uint32_t* root, int* __restrict__ changed) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t r = root[i];
+    uint32_t rr = root[r];
+    if (rr != r) { root[i] = rr; *changed = 1; }
+}
+__global__ void __launch_bounds__(256) k_lake_stats(uint32_t n, const int32_t* __restrict__ dh, const uint32_t* __restrict__ root,
+                                                    const double* __restrict__ h, uint32_t* __restrict__ size,
+                                                    unsigned long long* __restrict__ maxh_bits, uint32_t* __restrict__ counts) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    atomicAdd(size + root[i], 1u);
+    unsigned long long hb = (unsigned long long)__double_as_longlong(fabs(h[i])); // non-negative: bits are monotone
+    atomicMax(maxh_bits, hb);
+    int32_t d = dh[i];
+    if (d == -2) atomicAdd(counts + 0, 1u);
+    else if (d == -1) atomicAdd(counts + 1, 1u);
+}
+// Euler tour of the dh forest (children in ascending slot); every tree ends with END.
+__global__ void __launch_bounds__(256) k_tree_arcs(Geom g, const int32_t* __restrict__ dh, uint32_t* __restrict__ succ,
+                                                   int32_t* __restrict__ w0, int32_t* __restrict__ w1) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= g.n) return;
+    int x = g.x_of(v), y = g.y_of(v);
+    uint32_t first = 0xffffffffu;
+    for (int k = 0; k < 8; ++k) {
+        int xx = x + c_ndx[k], yy = y + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        uint32_t nb = g.idx(xx, yy);
+        if (dh[nb] == (int32_t)v) { first = nb; break; }
+    }
+    succ[2 * v] = first != 0xffffffffu ? 2 * first : 2 * v + 1;
+    w0[2 * v] = 1; w0[2 * v + 1] = 0; w1[2 * v] = 1; w1[2 * v + 1] = -1;
+    int32_t p = dh[v];
+    uint32_t nxt = 0xffffffffu;
+    if (p >= 0) {
+        int px = g.x_of((uint32_t)p), py = g.y_of((uint32_t)p);
+        int s = l_slot_of(x - px, y - py);
+        nxt = 2 * (uint32_t)p + 1;
+        for (int k = s + 1; k < 8; ++k) {
+            int xx = px + c_ndx[k], yy = py + c_ndy[k];
+            if (!g.inb(xx, yy)) continue;
+            uint32_t nb = g.idx(xx, yy);
+            if (dh[nb] == p) { nxt = 2 * nb; break; }
+        }
+    }
+    succ[2 * v + 1] = nxt;
+}
+// BFS-position key inside a tree: (depth, pre-order) ascending; 24 + 32 bits.
+__global__ void __launch_bounds__(256) k_bfs_key(uint32_t n, const int32_t* __restrict__ w0, const int32_t* __restrict__ w1,
+                                                 uint64_t* __restrict__ key, int* __restrict__ bad) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    // a tree's tour sums to 0, so the inclusive suffix of w1 at enter(v) is -depth(v)
+    int32_t depth = -w1[2 * v];
+    if (depth < 0 || depth >= (1 << 24)) { *bad = 1; depth = 0; }
+    uint32_t s = (uint32_t)w0[2 * v];
+    key[v] = ((uint64_t)(uint32_t)depth << 32) | (uint64_t)(0xffffffffu - s);
+}
+
+// ---- (ii) pass table ---------------------------------------------------------------------------
+struct PassTable { uint64_t* key; unsigned long long* hb; unsigned long long* tie; uint64_t* edge; uint32_t mask; };
+
+__device__ __forceinline__ uint32_t pt_find_or_insert(const PassTable& t, uint64_t k) {
+    uint32_t s = (uint32_t)l_hash(k) & t.mask;
+    for (;;) {
+        unsigned long long cur = atomicCAS((unsigned long long*)t.key + s, 0ull, (unsigned long long)k);
+        if (cur == 0ull || cur == k) return s;
+        s = (s + 1) & t.mask;
+    }
+}
+__device__ __forceinline__ uint32_t pt_find(const PassTable& t, uint64_t k) {
+    uint32_t s = (uint32_t)l_hash(k) & t.mask;
+    while (t.key[s] != k) s = (s + 1) & t.mask;
+    return s;
+}
+// mode 0: count cross edges; 1: min height; 2: min tie key; 3: write edge
+__global__ void __launch_bounds__(256) k_pass_scan(Geom g, int mode, const double* __restrict__ h, const int32_t* __restrict__ dh0,
+                                                   const uint32_t* __restrict__ root, const uint64_t* __restrict__ bfskey,
+                                                   PassTable t, uint32_t* __restrict__ counter) {
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= g.n) return;
+    uint32_t A = root[c];
+    bool a_boundary = dh0[A] == -2;
+    int x = g.x_of(c), y = g.y_of(c);
+    double hc = h[c];
+    for (int k = 0; k < 8; ++k) {
+        int xx = x + c_ndx[k], yy = y + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        uint32_t nb = g.idx(xx, yy);
+        uint32_t B = root[nb];
+        if (!(B < A)) continue;                       // 1934: only the higher-offset lake's cell scans
+        if (a_boundary && dh0[B] == -2) continue;     // boundary-boundary passes are deleted in (iii)
+        if (mode == 0) { atomicAdd(counter, 1u); continue; }
+        uint64_t pk = (((uint64_t)A << 32) | (uint64_t)B) + 1ull;
+        unsigned long long hb = l_order_bits(fmax(hc, h[nb]));
+        if (mode == 1) {
+            uint32_t s = pt_find_or_insert(t, pk);
+            atomicMin(t.hb + s, hb);
+        } else {
+            uint32_t s = pt_find(t, pk);
+            if (t.hb[s] != hb) continue;
+            unsigned long long tk = (bfskey[c] << 3) | (unsigned long long)k;
+            if (mode == 2) atomicMin(t.tie + s, tk);
+            else if (t.tie[s] == tk) t.edge[s] = ((uint64_t)c << 32) | (uint64_t)nb;
+        }
+    }
+}
+
+// lake ranks: non-boundary lake roots in ascending index
+__global__ void __launch_bounds__(256) k_lake_flags(uint32_t n, const int32_t* __restrict__ dh0, uint32_t* __restrict__ fl) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) fl[i] = dh0[i] == -1 ? 1u : 0u;
+}
+// adjacency degree / fill over the table; also emits the initial candidates (edges into boundary lakes)
+__global__ void __launch_bounds__(256) k_adj_build(uint32_t cap, int fill, PassTable t, const int32_t* __restrict__ dh0,
+                                                   const uint32_t* __restrict__ lrank, const uint32_t* __restrict__ off,
+                                                   uint32_t* __restrict__ deg, uint64_t* __restrict__ adj,
+                                                   uint64_t* __restrict__ cand_k0, uint64_t* __restrict__ cand_k1,
+                                                   uint32_t* __restrict__ counter) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= cap || t.key[s] == 0) return;
+    uint64_t pk = t.key[s] - 1ull;
+    uint32_t A = (uint32_t)(pk >> 32), B = (uint32_t)pk;
+    uint64_t e = t.edge[s];
+    uint32_t ca = (uint32_t)(e >> 32), cb = (uint32_t)e;
+    bool an = dh0[A] == -1, bn = dh0[B] == -1;
+    if (an) {
+        uint32_t i = atomicAdd(deg + lrank[A], 1u);
+        if (fill) adj[off[lrank[A]] + i] = ((uint64_t)ca << 32) | cb;
+    }
+    if (bn) {
+        uint32_t i = atomicAdd(deg + lrank[B], 1u);
+        if (fill) adj[off[lrank[B]] + i] = ((uint64_t)cb << 32) | ca;
+    }
+    if (fill && (an != bn)) { // exactly one side is a boundary lake: 2057-2064
+        uint32_t i = atomicAdd(counter, 1u);
+        cand_k0[i] = t.hb[s];
+        cand_k1[i] = an ? (((uint64_t)ca << 32) | cb) : (((uint64_t)cb << 32) | ca);
+    }
+}
+
+// ---- (iv) Prim growth, one warp ------------------------------------------------------------------
+// 32-ary min-heap on (k0, k1); heap arrays hold `hn` entries.
+__device__ __forceinline__ bool key_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1) {
+    return a0 < b0 || (a0 == b0 && a1 < b1);
+}
+__global__ void __launch_bounds__(32) k_lake_connect(const double* __restrict__ h, const int32_t* __restrict__ dh0,
+                                                     const uint32_t* __restrict__ root, const uint32_t* __restrict__ lrank,
+                                                     const uint32_t* __restrict__ off, const uint64_t* __restrict__ adj,
+                                                     uint64_t* hk0, uint64_t* hk1, uint32_t hn0, int32_t* dh,
+                                                     int32_t* indirection, uint8_t* connected, uint32_t* __restrict__ flows,
+                                                     uint32_t* __restrict__ n_flows_out) {
+    const unsigned lane = threadIdx.x;
+    uint32_t hn = hn0, n_flows = 0;
+    while (hn > 0) {
+        // pop
+        uint64_t m1 = hk1[0];
+        hn--;
+        if (hn > 0) {
+            uint64_t l0 = hk0[hn], l1 = hk1[hn];
+            uint32_t i = 0;
+            for (;;) { // sift down: the 32 children of i are scanned by the lanes
+                uint32_t c = 32u * i + 1u + lane;
+                uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t ci = c;
+                if (c < hn) { c0 = hk0[c]; c1 = hk1[c]; }
+                for (int o = 16; o > 0; o >>= 1) {
+                    uint64_t o0 = __shfl_xor_sync(0xffffffffu, c0, o), o1 = __shfl_xor_sync(0xffffffffu, c1, o);
+                    uint32_t oi = __shfl_xor_sync(0xffffffffu, ci, o);
+                    if (key_less(o0, o1, c0, c1) || (o0 == c0 && o1 == c1 && oi < ci)) { c0 = o0; c1 = o1; ci = oi; }
+                }
+                if (32u * i + 1u >= hn || !key_less(c0, c1, l0, l1)) break;
+                if (lane == 0) { hk0[i] = c0; hk1[i] = c1; }
+                i = ci;
+            }
+            if (lane == 0) { hk0[i] = l0; hk1[i] = l1; }
+            __syncwarp();
+        }
+        uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
+        uint32_t lake = root[from];
+        uint32_t lr = lrank[lake];
+        if (connected[lr]) continue;                                  // 2085
+        __syncwarp();
+        if (lane == 0) {
+            connected[lr] = 1;
+            dh[lake] = (int32_t)to;                                   // 2098
+            indirection[lake] = -(int32_t)from;                       // 2103
+            flows[n_flows] = lake;                                    // 2105
+        }
+        n_flows++;
+        __syncwarp();
+        // push the reversed other passes of this lake (2107-2136)
+        uint32_t b = off[lr], e = off[lr + 1];
+        for (uint32_t a = b; a < e; ++a) {
+            uint64_t ed = adj[a];
+            uint32_t ef = (uint32_t)(ed >> 32), et = (uint32_t)ed;
+            if (ef == from && et == to) continue;
+            uint32_t tl = root[et];
+            if (dh0[tl] != -1) continue;                              // boundary lake
+            if (connected[lrank[tl]]) continue;                       // already handled
+            uint64_t k0 = l_order_bits(fmax(h[ef], h[et]));
+            uint64_t k1 = ((uint64_t)et << 32) | (uint64_t)ef;
+            if (lane == 0) { // sift up
+                uint32_t i = hn;
+                while (i > 0) {
+                    uint32_t p = (i - 1u) / 32u;
+                    if (!key_less(k0, k1, hk0[p], hk1[p])) break;
+                    hk0[i] = hk0[p]; hk1[i] = hk1[p];
+                    i = p;
+                }
+                hk0[i] = k0; hk1[i] = k1;
+            }
+            hn++;
+            __syncwarp();
+        }
+    }
+    if (lane == 0) *n_flows_out = n_flows;
+}
+
+// ---- (v) per-lake flood -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_lake_fill(Geom g, uint32_t n_flows, const uint32_t* __restrict__ flows,
+                                                   const double* __restrict__ h, const uint32_t* __restrict__ root,
+                                                   const uint32_t* __restrict__ start, int32_t* dh, const int32_t* __restrict__ indirection,
+                                                   uint8_t* tag, uint32_t* stack, int* __restrict__ bad) {
+    uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_flows) return;
+    const uint32_t chunk = flows[li];
+    const uint32_t nbr_pass = (uint32_t)dh[chunk];
+    const int32_t pass_s = -indirection[chunk];
+    if (pass_s < 0) { *bad = 1; return; }
+    const uint32_t pass = (uint32_t)pass_s;
+    uint32_t* st = stack + start[chunk];
+    uint32_t sp = 0;
+    st[sp++] = pass;
+    tag[pass] = 1; // InQueue
+    const int ox = g.x_of(nbr_pass), oy = g.y_of(nbr_pass);
+    const double elev = fmax(h[nbr_pass], h[pass]);
+    while (sp > 0) {
+        uint32_t node = st[--sp];
+        int cx = g.x_of(node), cy = g.y_of(node);
+        int64_t rcv = -1;
+        double rcv_cost = -INFINITY;
+        double odx = (double)(ox - cx), ody = (double)(oy - cy);
+        for (int k = 0; k < 8; ++k) {
+            int xx = cx + c_ndx[k], yy = cy + c_ndy[k];
+            if (!g.inb(xx, yy)) continue;
+            uint32_t nb = g.idx(xx, yy);
+            bool mine = root[nb] == chunk;           // indirection[nb] == chunk || nb == chunk
+            if ((!mine && nb != nbr_pass) || h[nb] > elev) continue;
+            // tags of foreign cells are never written here; the outflow cell counts as WithRcv (2212)
+            uint8_t tg = (nb == nbr_pass) ? (uint8_t)2 : tag[nb];
+            if (tg == 2) {
+                double ddx = (double)c_ndx[k], ddy = (double)c_ndy[k];
+                double mag = vm_sqrt(ddx * ddx + ddy * ddy);
+                double cost = odx * (ddx / mag) + ody * (ddy / mag);
+                if (cost > rcv_cost) { rcv = (int64_t)nb; rcv_cost = cost; }
+            } else if (tg == 0) {
+                st[sp++] = nb;
+                tag[nb] = 1;
+            }
+        }
+        if (rcv < 0) { *bad = 1; return; }            // assert_ne 2262
+        dh[node] = (int32_t)rcv;
+        tag[node] = 2;
+    }
+}
+
+// ---- final order ------------------------------------------------------------------------------------
+// Blocks: boundary roots (ascending index) then connected lakes in connection order.  Arc ids:
+// real node v -> 2v, 2v+1; virtual root of lake with rank r -> 2(n+r), 2(n+r)+1.
+__global__ void __launch_bounds__(256) k_final_arcs(Geom g, const int32_t* __restrict__ dh, const int32_t* __restrict__ dh0,
+                                                    const uint32_t* __restrict__ root, const uint32_t* __restrict__ lrank,
+                                                    const uint32_t* __restrict__ block_of_root, const uint32_t* __restrict__ block_head,
+                                                    uint32_t n_blocks, uint32_t* __restrict__ succ, int32_t* __restrict__ w0,
+                                                    int32_t* __restrict__ w1) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= g.n) return;
+    const uint32_t n = g.n;
+    int x = g.x_of(v), y = g.y_of(v);
+    uint32_t lake = root[v];
+    // first child inside the same lake
+    uint32_t first = 0xffffffffu;
+    for (int k = 0; k < 8; ++k) {
+        int xx = x + c_ndx[k], yy = y + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        uint32_t nb = g.idx(xx, yy);
+        if (dh[nb] == (int32_t)v && root[nb] == lake) { first = nb; break; }
+    }
+    succ[2 * v] = first != 0xffffffffu ? 2 * first : 2 * v + 1;
+    w0[2 * v] = 1; w0[2 * v + 1] = 0; w1[2 * v] = 1; w1[2 * v + 1] = -1;
+    int32_t p = dh[v];
+    uint32_t nxt;
+    if (p < 0) { // ocean root: block root
+        uint32_t bi = block_of_root[v];
+        nxt = (bi + 1 < n_blocks) ? block_head[bi + 1] : 0xffffffffu;
+    } else {
+        bool same = root[(uint32_t)p] == lake;
+        uint32_t up = same ? (2 * (uint32_t)p + 1) : (2 * (n + lrank[lake]) + 1);
+        int px = g.x_of((uint32_t)p), py = g.y_of((uint32_t)p);
+        int s = l_slot_of(x - px, y - py);
+        nxt = up;
+        for (int k = s + 1; k < 8; ++k) {
+            int xx = px + c_ndx[k], yy = py + c_ndy[k];
+            if (!g.inb(xx, yy)) continue;
+            uint32_t nb = g.idx(xx, yy);
+            if (dh[nb] == p && root[nb] == lake) { nxt = 2 * nb; break; }
+        }
+    }
+    succ[2 * v + 1] = nxt;
+}
+__global__ void __launch_bounds__(256) k_final_virtual(Geom g, uint32_t n_flows, const uint32_t* __restrict__ flows,
+                                                       const int32_t* __restrict__ dh, const uint32_t* __restrict__ root,
+                                                       const uint32_t* __restrict__ lrank, const uint32_t* __restrict__ block_of_root,
+                                                       const uint32_t* __restrict__ block_head, uint32_t n_blocks,
+                                                       uint32_t* __restrict__ succ, int32_t* __restrict__ w0, int32_t* __restrict__ w1) {
+    uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_flows) return;
+    uint32_t chunk = flows[li];
+    uint32_t a = 2 * (g.n + lrank[chunk]);
+    w0[a] = 0; w0[a + 1] = 0; w1[a] = 1; w1[a + 1] = -1;
+    uint32_t bi = block_of_root[chunk];
+    succ[a + 1] = (bi + 1 < n_blocks) ? block_head[bi + 1] : 0xffffffffu;
+}
+// first child of each virtual root: neighbours of the outflow cell, ascending slot, in this lake
+__global__ void __launch_bounds__(256) k_final_virtual_first(Geom g, uint32_t n_flows, const uint32_t* __restrict__ flows,
+                                                             const uint32_t* __restrict__ outflow, const int32_t* __restrict__ dh,
+                                                             const uint32_t* __restrict__ root, const uint32_t* __restrict__ lrank,
+                                                             uint32_t* __restrict__ succ) {
+    uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_flows) return;
+    uint32_t chunk = flows[li];
+    uint32_t a = 2 * (g.n + lrank[chunk]);
+    uint32_t p = outflow[li];
+    int px = g.x_of(p), py = g.y_of(p);
+    uint32_t first = 0xffffffffu;
+    for (int k = 0; k < 8; ++k) {
+        int xx = px + c_ndx[k], yy = py + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        uint32_t nb = g.idx(xx, yy);
+        if (dh[nb] == (int32_t)p && root[nb] == chunk) { first = nb; break; }
+    }
+    succ[a] = first != 0xffffffffu ? 2 * first : a + 1;
+}
+__global__ void __launch_bounds__(256) k_save_outflow(uint32_t n_flows, const uint32_t* __restrict__ flows, const int32_t* __restrict__ dh,
+                                                      uint32_t* __restrict__ outflow) {
+    uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li < n_flows) outflow[li] = (uint32_t)dh[flows[li]];
+}
+// block bookkeeping
+__global__ void __launch_bounds__(256) k_boundary_flags(uint32_t n, const int32_t* __restrict__ dh0, uint32_t* __restrict__ fl) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) fl[i] = dh0[i] == -2 ? 1u : 0u;
+}
+__global__ void __launch_bounds__(256) k_blocks_boundary(uint32_t n, const int32_t* __restrict__ dh0, const uint32_t* __restrict__ brank,
+                                                         uint32_t* __restrict__ block_of_root, uint32_t* __restrict__ block_head) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || dh0[i] != -2) return;
+    block_of_root[i] = brank[i];
+    block_head[brank[i]] = 2 * i;
+}
+__global__ void __launch_bounds__(256) k_blocks_lakes(uint32_t n, uint32_t n_boundary, uint32_t n_flows, const uint32_t* __restrict__ flows,
+                                                      const uint32_t* __restrict__ lrank, uint32_t* __restrict__ block_of_root,
+                                                      uint32_t* __restrict__ block_head) {
+    uint32_t li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= n_flows) return;
+    uint32_t chunk = flows[li];
+    block_of_root[chunk] = n_boundary + li;
+    block_head[n_boundary + li] = 2 * (n + lrank[chunk]);
+}
+__global__ void __launch_bounds__(256) k_final_keys(uint32_t n, const int32_t* __restrict__ w0, const int32_t* __restrict__ w1,
+                                                    const uint32_t* __restrict__ root, const uint32_t* __restrict__ block_of_root,
+                                                    uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int* __restrict__ bad) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    int64_t t = (int64_t)n - (int64_t)w0[2 * v];
+    int32_t depth = -w1[2 * v];
+    if (t < 0 || t >= (int64_t)n || depth < 0) { *bad = 1; return; }
+    keys[t] = ((uint64_t)block_of_root[root[v]] << 32) | (uint64_t)(uint32_t)depth;
+    vals[t] = v;
+}
+__global__ void __launch_bounds__(256) k_indirection(uint32_t n, const int32_t* __restrict__ dh0, const uint32_t* __restrict__ root,
+                                                     const uint32_t* __restrict__ size, int32_t* __restrict__ ind) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ind[i] = dh0[i] < 0 ? -(int32_t)(8u * size[i]) : (int32_t)root[i];   // 1891, 1900
+}
+
+int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh) {
+    const Geom& g = ctx->g;
+    const uint32_t n = g.n;
+    const unsigned nb = ve_blocks(n, 256);
+    cudaStream_t st = ctx->stream;
+    // persistent per-call arrays live in the forest scratch of the context
+    uint32_t* root = ctx->f_root;       // original lake root of every cell
+    uint32_t* size = ctx->f_depth;      // tree size (valid at roots)
+    uint32_t* lrank = ctx->f_jump;      // rank of non-boundary lake roots / boundary ranks later
+    int32_t* dh0 = ctx->dh0;            // receivers before lake resolution
+    VE_CUDA(cudaMemcpyAsync(dh0, dh, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    uint32_t* small;                    // [0] boundary count [1] lake count [2] cross edges [3] cand count [4] n_flows [6..7] maxh bits, [8] changed, [9] bad
+    VE_TRY(ve_scratch(ctx, 3, 4096, (void**)&small));
+    VE_CUDA(cudaMemsetAsync(small, 0, 4096, st));
+    int* changed = (int*)(small + 8);
+    int* bad = (int*)(small + 9);
+    // (i) roots by pointer jumping
+    k_root_init<<<nb, 256, 0, st>>>(n, dh0, root);
+    VE_LAUNCH_CHECK();
+    for (int round = 0; round < 64; ++round) {
+        VE_CUDA(cudaMemsetAsync(changed, 0, 4, st));
+        for (int r = 0; r < 3; ++r) { k_root_jump<<<nb, 256, 0, st>>>(n, root, changed); VE_LAUNCH_CHECK(); }
+        int hc = 0;
+        VE_CUDA(cudaMemcpyAsync(&hc, changed, 4, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        if (!hc) break;
+    }
+    VE_CUDA(cudaMemsetAsync(size, 0, (size_t)n * 4, st));
+    k_lake_stats<<<nb, 256, 0, st>>>(n, dh0, root, h, size, (unsigned long long*)(small + 6), small);
+    VE_LAUNCH_CHECK();
+    k_indirection<<<nb, 256, 0, st>>>(n, dh0, root, size, indirection);
+    VE_LAUNCH_CHECK();
+    // BFS keys of the dh0 forest
+    uint32_t* succ; int32_t *w0, *w1; uint64_t* bfskey;
+    VE_TRY(ve_scratch(ctx, 0, ((size_t)n * 2 + 64) * 4 * 2, (void**)&succ));   // sized for the final tour too
+    VE_TRY(ve_scratch(ctx, 1, ((size_t)n * 2 + 64) * 4 * 2, (void**)&w0));
+    VE_TRY(ve_scratch(ctx, 2, ((size_t)n * 2 + 64) * 4 * 2, (void**)&w1));
+    VE_TRY(ve_scratch(ctx, 4, (size_t)n * 8, (void**)&bfskey));
+    k_tree_arcs<<<nb, 256, 0, st>>>(g, dh0, succ, w0, w1);
+    VE_LAUNCH_CHECK();
+    VE_TRY(ve_list_rank(ctx, 2 * n, succ, w0, w1));
+    k_bfs_key<<<nb, 256, 0, st>>>(n, w0, w1, bfskey, bad);
+    VE_LAUNCH_CHECK();
+    // lake ranks (non-boundary roots, ascending index)
+    uint32_t* flagbuf = (uint32_t*)w0; // reuse
+    size_t tmp_bytes = 0; void* tmp;
+    k_lake_flags<<<nb, 256, 0, st>>>(n, dh0, flagbuf);
+    VE_LAUNCH_CHECK();
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flagbuf, lrank, (int)n, st);
+    VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+    VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flagbuf, lrank, (int)n, st));
+    ctx->launches += 2;
+    // (ii) count cross edges, size the table
+    PassTable t{nullptr, nullptr, nullptr, nullptr, 0};
+    k_pass_scan<<<nb, 256, 0, st>>>(g, 0, h, dh0, root, bfskey, t, small + 2);
+    VE_LAUNCH_CHECK();
+    uint32_t hs[16];
+    VE_CUDA(cudaMemcpyAsync(hs, small, 64, cudaMemcpyDeviceToHost, st));
+    VE_CUDA(cudaStreamSynchronize(st));
+    const uint32_t n_boundary = hs[0], n_lakes = hs[1], n_cross = hs[2];
+    { unsigned long long mb; memcpy(&mb, hs + 6, 8); double mh; memcpy(&mh, &mb, 8); ctx->maxh = mh; }
+    ctx->boundary_len = n_boundary; ctx->n_lakes = n_lakes;
+    if (hs[9]) { ctx->err = "get_lakes: tree depth overflow"; return VE_ERR_TOO_LARGE; }
+    uint32_t n_flows = 0;
+    uint32_t *flows = nullptr, *outflow = nullptr;
+    VE_TRY(ve_scratch(ctx, 5, ((size_t)n_lakes + 1) * 4 * 2, (void**)&flows));
+    outflow = flows + n_lakes + 1;
+    if (n_lakes > 0) {
+        uint32_t cap = 64;
+        while (cap < 2 * n_cross + 2) cap <<= 1;
+        uint8_t* tbl;
+        VE_TRY(ve_scratch(ctx, 6, (size_t)cap * 32, (void**)&tbl));
+        t.key = (uint64_t*)tbl; t.hb = (unsigned long long*)(tbl + (size_t)cap * 8);
+        t.tie = (unsigned long long*)(tbl + (size_t)cap * 16); t.edge = (uint64_t*)(tbl + (size_t)cap * 24);
+        t.mask = cap - 1;
+        VE_CUDA(cudaMemsetAsync(t.key, 0, (size_t)cap * 8, st));
+        VE_CUDA(cudaMemsetAsync(t.hb, 0xff, (size_t)cap * 16, st)); // hb and tie = max
+        for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
+        // adjacency (CSR over non-boundary lakes)
+        uint32_t *deg, *off; uint64_t *adj, *ck0, *ck1, *ck0s, *ck1s;
+        size_t lk = (size_t)n_lakes + 1;
+        uint8_t* ab;
+        size_t adj_cap = 2 * (size_t)n_cross + 2;
+        VE_TRY(ve_scratch(ctx, 7, lk * 8 + adj_cap * 8 * 5 + 256, (void**)&ab));
+        deg = (uint32_t*)ab; off = deg + lk;
+        adj = (uint64_t*)(ab + ((lk * 8 + 15) / 16) * 16);
+        ck0 = adj + adj_cap; ck1 = ck0 + adj_cap; ck0s = ck1 + adj_cap; ck1s = ck0s + adj_cap;
+        VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 0, t, dh0, lrank, off, deg, adj, ck0, ck1, small + 3);
+        VE_LAUNCH_CHECK();
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, deg, off, (int)lk, st);
+        VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+        VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, deg, off, (int)lk, st));
+        ctx->launches += 2;
+        VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj, ck0, ck1, small + 3);
+        VE_LAUNCH_CHECK();
+        uint32_t n_cand = 0;
+        VE_CUDA(cudaMemcpyAsync(&n_cand, small + 3, 4, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        // initial heap = candidates sorted by (k0, k1): LSD passes, k1 first
+        uint64_t *h0 = ck0, *h1 = ck1;
+        if (n_cand > 1) {
+            cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck1, ck1s, ck0, ck0s, (int)n_cand, 0, 64, st);
+            VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck1, ck1s, ck0, ck0s, (int)n_cand, 0, 64, st));
+            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0s, ck0, ck1s, ck1, (int)n_cand, 0, 64, st));
+            ctx->launches += 8;
+        }
+        uint8_t* connected;
+        VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
+        VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
+        k_lake_connect<<<1, 32, 0, st>>>(h, dh0, root, lrank, off, adj, h0, h1, n_cand, dh, indirection, connected, flows, small + 4);
+        VE_LAUNCH_CHECK();
+        VE_CUDA(cudaMemcpyAsync(&n_flows, small + 4, 4, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
+        // (v) flood: per-lake stacks carved out of one array by an exclusive scan of tree sizes
+        k_save_outflow<<<ve_blocks(n_flows, 256), 256, 0, st>>>(n_flows, flows, dh, outflow);
+        VE_LAUNCH_CHECK();
+        uint32_t* start = (uint32_t*)w1; uint32_t* stack = (uint32_t*)w1 + n; uint8_t* tag = (uint8_t*)w0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, size, start, (int)n, st);
+        VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+        VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, size, start, (int)n, st));
+        ctx->launches += 2;
+        VE_CUDA(cudaMemsetAsync(tag, 0, n, st));
+        k_lake_fill<<<ve_blocks(n_flows, 128), 128, 0, st>>>(g, n_flows, flows, h, root, start, dh, indirection, tag, stack, bad);
+        VE_LAUNCH_CHECK();
+    }
+    // final order: blocks, Euler tour with virtual lake roots, ranking, stable sort by (block, depth)
+    uint32_t n_blocks = n_boundary + n_flows;
+    uint32_t *brank = (uint32_t*)bfskey /*scratch 4 (>= 8n bytes)*/, *block_of_root = brank + n;
+    uint32_t* block_head;
+    VE_TRY(ve_scratch(ctx, 6, ((size_t)n_blocks + 1) * 4, (void**)&block_head));
+    uint32_t* flagbuf2 = (uint32_t*)w0;
+    k_boundary_flags<<<nb, 256, 0, st>>>(n, dh0, flagbuf2);
+    VE_LAUNCH_CHECK();
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flagbuf2, brank, (int)n, st);
+    VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+    VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flagbuf2, brank, (int)n, st));
+    ctx->launches += 2;
+    k_blocks_boundary<<<nb, 256, 0, st>>>(n, dh0, brank, block_of_root, block_head);
+    VE_LAUNCH_CHECK();
+    if (n_flows > 0) {
+        k_blocks_lakes<<<ve_blocks(n_flows, 256), 256, 0, st>>>(n, n_boundary, n_flows, flows, lrank, block_of_root, block_head);
+        VE_LAUNCH_CHECK();
+    }
+    uint32_t n_arcs = 2 * (n + n_lakes);
+    k_final_arcs<<<nb, 256, 0, st>>>(g, dh, dh0, root, lrank, block_of_root, block_head, n_blocks, succ, w0, w1);
+    VE_LAUNCH_CHECK();
+    if (n_flows > 0) {
+        unsigned fb = ve_blocks(n_flows, 256);
+        k_final_virtual<<<fb, 256, 0, st>>>(g, n_flows, flows, dh, root, lrank, block_of_root, block_head, n_blocks, succ, w0, w1);
+        VE_LAUNCH_CHECK();
+        k_final_virtual_first<<<fb, 256, 0, st>>>(g, n_flows, flows, outflow, dh, root, lrank, succ);
+        VE_LAUNCH_CHECK();
+    }
+    VE_TRY(ve_list_rank(ctx, n_arcs, succ, w0, w1));
+    uint64_t *keys = (uint64_t*)succ, *keys_out; uint32_t *vals, *vals_out = newh;
+    VE_TRY(ve_scratch(ctx, 6, (size_t)n * 8, (void**)&keys_out));
+    VE_TRY(ve_scratch(ctx, 7, (size_t)n * 4, (void**)&vals));
+    VE_CUDA(cudaMemsetAsync(vals, 0xff, (size_t)n * 4, st));
+    k_final_keys<<<nb, 256, 0, st>>>(n, w0, w1, root, block_of_root, keys, vals, bad);
+    VE_LAUNCH_CHECK();
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_out, vals, vals_out, (int)n, 0, 64, st);
+    VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+    VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_out, vals, vals_out, (int)n, 0, 64, st));
+    ctx->launches += 4;
+    int hbad = 0;
+    VE_CUDA(cudaMemcpyAsync(&hbad, bad, 4, cudaMemcpyDeviceToHost, st));
+    VE_CUDA(cudaStreamSynchronize(st));
+    if (hbad) { ctx->err = "get_lakes: inconsistent lake graph"; return VE_ERR_LAKE_GRAPH; }
+    return VE_OK;
+}

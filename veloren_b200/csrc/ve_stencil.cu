@@ -1,0 +1,436 @@
+// ve_stencil.cu — the per-cell (stencil / map) stages of erode() as sm_100a kernels.
+// Each kernel cites the reference lines whose arithmetic it reproduces operation by operation
+// (device code is built with --fmad=false so a*b+c is never contracted, as in Rust).
+#include "ve_internal.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// E1: D8 receivers.  util.rs:251-279; ocean predicate of erosion.rs:818 when use_h_le0 != 0.
+__global__ void __launch_bounds__(256) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
+                                                  int use_h_le0, int32_t* __restrict__ dh) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    double nh = h[posi];
+    bool oc = ocean[posi] != 0;
+    if (use_h_le0) oc = oc && (nh <= 0.0);
+    if (oc) { dh[posi] = -2; return; }
+    int x = g.x_of(posi), y = g.y_of(posi);
+    int best = -1; double besth = nh;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        int xx = x + c_ndx[k], yy = y + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        uint32_t np = g.idx(xx, yy);
+        double nbh = h[np];
+        if (nbh < besth) { besth = nbh; best = (int)np; }
+    }
+    dh[posi] = best;
+}
+
+int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh) {
+    k_downhill<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E3b/E3c: receiver mask, donor count and MFD weights.  erosion.rs:2407-2439, 2444-2479.
+__global__ void __launch_bounds__(256) k_mrec(Geom g, const double* __restrict__ wh, uint8_t* __restrict__ mrec,
+                                              uint8_t* __restrict__ ndon, double* __restrict__ mwrec) {
+    uint32_t ij = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ij >= g.n) return;
+    const double SQ = vm_sqrt(32.0 * 32.0 + 32.0 * 32.0);
+    double wh_ij = wh[ij];
+    int x = g.x_of(ij), y = g.y_of(ij);
+    unsigned mr = 0, nd = 0;
+    double wrec[8];
+    double sumweight = 0.0; int nrec = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        wrec[k] = 0.0;
+        int xx = x + c_ndx[k], yy = y + c_ndy[k];
+        if (!g.inb(xx, yy)) continue;
+        double wh_ijk = wh[g.idx(xx, yy)];
+        if (wh_ij > wh_ijk) {
+            mr |= 1u << k;
+            double lrec = (c_ndx[k] != 0 && c_ndy[k] != 0) ? SQ : 32.0;
+            double w = (wh_ij - wh_ijk) / lrec;
+            wrec[k] = w; sumweight += w; nrec += 1;
+        } else if (wh_ijk > wh_ij) nd += 1;
+    }
+    mrec[ij] = (uint8_t)mr; ndon[ij] = (uint8_t)nd;
+    double slope = sumweight / fmax((double)nrec, 1.0);
+    double p_mfd_exp = 0.5 + 0.6 * slope;
+    sumweight = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        double w = vm_pow(wrec[k], p_mfd_exp);
+        sumweight += w; wrec[k] = w;
+    }
+    if (sumweight > 0.0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) wrec[k] /= sumweight;
+    }
+    double2* out = reinterpret_cast<double2*>(mwrec + (size_t)ij * 8);
+    out[0] = make_double2(wrec[0], wrec[1]); out[1] = make_double2(wrec[2], wrec[3]);
+    out[2] = make_double2(wrec[4], wrec[5]); out[3] = make_double2(wrec[6], wrec[7]);
+}
+
+int ve_k_mrec(ve_ctx* ctx) {
+    k_mrec<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->wh, ctx->mrec, ctx->ndon, ctx->mwrec);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E5: critical slope from Fbm<Perlin> rock strength.  erosion.rs:550-604; noise 0.9.0
+// perlin_3d / Fbm::get restated (crate source is not in the reference tree).
+__device__ __forceinline__ double d_grad3(unsigned hsh, double x, double y, double z) {
+    switch (hsh & 15u) {
+        case 0: return x + y;   case 1: return -x + y;  case 2: return x - y;   case 3: return -x - y;
+        case 4: return x + z;   case 5: return -x + z;  case 6: return x - z;   case 7: return -x - z;
+        case 8: return y + z;   case 9: return -y + z;  case 10: return y - z;  case 11: return -y - z;
+        case 12: return x + y;  case 13: return -x + y; case 14: return -y + z; default: return -y - z;
+    }
+}
+__device__ __forceinline__ double d_quintic(double t) { return t * t * t * (t * (t * 6.0 - 15.0) + 10.0); }
+
+__device__ double d_perlin3(const uint8_t* p, double px, double py, double pz) {
+    double fx = floor(px), fy = floor(py), fz = floor(pz);
+    long long ix = (long long)fx, iy = (long long)fy, iz = (long long)fz;
+    double dx = px - fx, dy = py - fy, dz = pz - fz;
+    unsigned x0 = (unsigned)(ix & 0xff), x1 = (unsigned)((ix + 1) & 0xff);
+    unsigned y0 = (unsigned)(iy & 0xff), y1 = (unsigned)((iy + 1) & 0xff);
+    unsigned z0 = (unsigned)(iz & 0xff), z1 = (unsigned)((iz + 1) & 0xff);
+    unsigned a0 = p[x0], a1 = p[x1];
+    unsigned b00 = p[a0 ^ y0], b10 = p[a1 ^ y0], b01 = p[a0 ^ y1], b11 = p[a1 ^ y1];
+    double g000 = d_grad3(p[b00 ^ z0], dx, dy, dz);
+    double g100 = d_grad3(p[b10 ^ z0], dx - 1.0, dy, dz);
+    double g010 = d_grad3(p[b01 ^ z0], dx, dy - 1.0, dz);
+    double g110 = d_grad3(p[b11 ^ z0], dx - 1.0, dy - 1.0, dz);
+    double g001 = d_grad3(p[b00 ^ z1], dx, dy, dz - 1.0);
+    double g101 = d_grad3(p[b10 ^ z1], dx - 1.0, dy, dz - 1.0);
+    double g011 = d_grad3(p[b01 ^ z1], dx, dy - 1.0, dz - 1.0);
+    double g111 = d_grad3(p[b11 ^ z1], dx - 1.0, dy - 1.0, dz - 1.0);
+    double u = d_quintic(dx), v = d_quintic(dy), w = d_quintic(dz);
+    double k0 = g000;
+    double k1 = g100 - g000;
+    double k2 = g010 - g000;
+    double k3 = g001 - g000;
+    double k4 = g000 + g110 - g100 - g010;
+    double k5 = g000 + g101 - g100 - g001;
+    double k6 = g000 + g011 - g010 - g001;
+    double k7 = g100 + g010 + g001 + g111 - g110 - g101 - g011 - g000;
+    double r = k0 + k1 * u + k2 * v + k3 * w + k4 * u * v + k5 * u * w + k6 * v * w + k7 * u * v * w;
+    r = r * 1.1547005383792515;
+    return fmin(1.0, fmax(-1.0, r));
+}
+
+__global__ void __launch_bounds__(256) k_max_slope(Geom g, ve_params P, NoiseDev nz, const double* __restrict__ h,
+                                                   const double* __restrict__ hscale, double* __restrict__ out,
+                                                   double* __restrict__ h_t) {
+    extern __shared__ uint8_t s_perm[];
+    for (unsigned i = threadIdx.x; i < nz.octaves * 256u; i += blockDim.x) s_perm[i] = nz.perm[i];
+    __syncthreads();
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    const double max_angle_range = P.max_max_angle - P.min_max_angle;
+    const double logistic_2_base = vm_sqrt(3.0) * 0.63661977236758134308;
+    const double center = 0.4, dmin = center - 0.05, dmax = center + 0.05;
+    const double logit_center = vm_log(center) - vm_log1p(-center);
+    double z = h[posi];
+    h_t[posi] = z; // erosion.rs:854 h.to_vec()
+    double px = (double)g.x_of(posi) * 32.0, py = (double)g.y_of(posi) * 32.0;
+    double wposz = z / hscale[posi];
+    double div_factor = (2.0 * 32.0) / 8.0;
+    double pz = wposz * div_factor;
+    // Fbm::get
+    double result = 0.0, attenuation = nz.persistence;
+    px *= nz.frequency; py *= nz.frequency; pz *= nz.frequency;
+    for (uint32_t o = 0; o < nz.octaves; ++o) {
+        double signal = d_perlin3(s_perm + o * 256u, px, py, pz);
+        signal *= attenuation;
+        attenuation *= nz.persistence;
+        result += signal;
+        px *= nz.lacunarity; py *= nz.lacunarity; pz *= nz.lacunarity;
+    }
+    double rs = result * nz.scale_factor;
+    rs = fmin(1.0, fmax(-1.0, rs)) * 0.5 + 0.5;
+    double a = fmin(1.0 - 1e-7, fmax(1e-7, rs));
+    double hz = fabs(wposz / P.mountain_scale);
+    hz = fmin(dmax, fmax(dmin, hz));
+    double la = vm_log(a) - vm_log1p(-a);
+    double lh = vm_log(hz) - vm_log1p(-hz);
+    double arg = 1.0 * la + 1.0 * (lh - logit_center);
+    double rock = vm_tanh(arg / logistic_2_base) * 0.5 + 0.5;
+    out[posi] = rock * max_angle_range + P.min_max_angle;
+}
+
+int ve_k_max_slope(ve_ctx* ctx) {
+    size_t smem = (size_t)ctx->nz.octaves * 256;
+    k_max_slope<<<ve_blocks(ctx->g.n, 256), 256, smem, ctx->stream>>>(ctx->g, ctx->P, ctx->nz, ctx->h, ctx->hscale,
+                                                                      ctx->max_slope, ctx->h_t);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E6: stream-power factors, fused pair.  erosion.rs:870-1006.
+__global__ void __launch_bounds__(256) k_kfactors(Geom g, ve_params P, float max_uplift, const int32_t* __restrict__ dh,
+                                                  const double* __restrict__ b, const double* __restrict__ h_t,
+                                                  const float* __restrict__ nf, const float* __restrict__ mf,
+                                                  const double* __restrict__ kf, const float* __restrict__ gf,
+                                                  const float* __restrict__ uplift, const double* __restrict__ area,
+                                                  const double* __restrict__ max_slope, const uint8_t* __restrict__ mrec,
+                                                  const double* __restrict__ mwrec, float* __restrict__ kfs,
+                                                  float* __restrict__ kdf) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    float fs[8], df[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { fs[k] = 0.0f; df[k] = 0.0f; }
+    if (dh[posi] >= 0) {
+        const double dt = (double)max_uplift / 1e-3;
+        const double sediment_thickness = 1.0e-4 * dt;
+        const double chunk_area = 32.0 * 32.0, p = 1.0, q = 0.2, q_ = 1.5;
+        const double SQ = vm_sqrt(32.0 * 32.0 + 32.0 * 32.0);
+        double sed = h_t[posi] - b[posi];
+        double k_fs = kf[posi] / 1.0;
+        double kk_ = ((sed > sediment_thickness) ? (4.0 * k_fs) : k_fs) * dt;
+        double n = (double)nf[posi], m = (double)mf[posi];
+        double uplift_i = (double)uplift[posi];
+        double area_i = area[posi];
+        double ms = max_slope[posi];
+        float gfi = gf[posi];
+        double g_i = (sed > sediment_thickness) ? (double)(1.0f * gfi) : (double)gfi;
+        double r0 = ms / P.mid_slope;
+        double k_da = P.k_da * (r0 * r0);
+        double ms_pow = vm_pow(ms, q_);
+        unsigned mr = mrec[posi];
+        const double* w = mwrec + (size_t)posi * 8;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+            if (!((mr >> kk) & 1u)) continue;
+            double wk = w[kk];
+            double nd = (c_ndx[kk] != 0 && c_ndy[kk] != 0) ? SQ : 32.0;
+            double knew = kk_ * vm_pow(p * chunk_area * (area_i * wk), m) / vm_pow(nd, n);
+            fs[kk] = (float)knew;
+            double k = (wk * (uplift_i + (double)max_uplift * g_i / p)) / (1.0 + k_da * vm_pow(wk * 0.1e6, q)) / ms_pow;
+            double knew2 = k * (1.0 + k_da * P.chunk_area_pow_q * vm_pow(area_i * wk, q)) / vm_pow(nd, q_);
+            df[kk] = (float)knew2;
+        }
+    }
+    float4* o1 = reinterpret_cast<float4*>(kfs + (size_t)posi * 8);
+    float4* o2 = reinterpret_cast<float4*>(kdf + (size_t)posi * 8);
+    o1[0] = make_float4(fs[0], fs[1], fs[2], fs[3]); o1[1] = make_float4(fs[4], fs[5], fs[6], fs[7]);
+    o2[0] = make_float4(df[0], df[1], df[2], df[3]); o2[1] = make_float4(df[4], df[5], df[6], df[7]);
+}
+
+int ve_k_kfactors(ve_ctx* ctx) {
+    k_kfactors<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->P, ctx->max_uplift, ctx->dh, ctx->b,
+                                                                  ctx->h_t, ctx->nf, ctx->mf, ctx->kf, ctx->gf, ctx->uplift,
+                                                                  ctx->area, ctx->max_slope, ctx->mrec, ctx->mwrec,
+                                                                  ctx->kfs, ctx->kdf);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E10: basement + soil production (erosion.rs:1483-1531).  h is the post-solve height.
+__global__ void __launch_bounds__(256) k_basement(Geom g, float max_uplift, const double* __restrict__ h,
+                                                  double* __restrict__ b, const int32_t* __restrict__ dh,
+                                                  const float* __restrict__ uplift, const float* __restrict__ eps0,
+                                                  const float* __restrict__ alpha) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    const double dt = (double)max_uplift / 1e-3;
+    double h_i = h[posi];
+    double new_b_i = b[posi] + (double)uplift[posi];
+    int32_t posj = dh[posi];
+    double vertical_sed = fmax(h_i - new_b_i, 0.0);
+    double h_normal;
+    if (posj < 0) h_normal = vertical_sed;
+    else {
+        double h_j = h[posj];
+        double ex = (double)(g.x_of(posi) - g.x_of((uint32_t)posj)) * 32.0;
+        double ey = (double)(g.y_of(posi) - g.y_of((uint32_t)posj)) * 32.0;
+        double nd2 = ex * ex + ey * ey;
+        double dhh = h_i - h_j;
+        double h_i_fact = dhh / (nd2 + dhh * dhh);
+        double h_i_vertical = 1.0 - h_i_fact * dhh;
+        h_normal = vertical_sed * vm_sqrt(h_i_fact * h_i_fact * nd2 + h_i_vertical * h_i_vertical);
+    }
+    double p_i = (double)eps0[posi] * dt * vm_exp(-(double)alpha[posi] * h_normal);
+    new_b_i -= p_i;
+    new_b_i = fmin(new_b_i, h_i);
+    b[posi] = new_b_i;
+}
+
+// E11: lake silt (erosion.rs:1535-1556).  lake_silt / sill are grid-indexed here; lwv keeps the
+// reference's mixed index space (slot = the stored sill value).
+__global__ void __launch_bounds__(256) k_lake_silt(Geom g, double* __restrict__ h, const double* __restrict__ wh,
+                                                   const int32_t* __restrict__ sill, const double* __restrict__ lake_silt,
+                                                   const double* __restrict__ lwv) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    int32_t lposi = sill[posi];
+    if (lposi >= 0) {
+        double vol = lwv[lposi];
+        if (vol > 0.0) {
+            double hv = h[posi];
+            hv += fmax(0.0, fmin(lake_silt[posi], vol)) / vol * (wh[posi] - hv);
+            h[posi] = hv;
+        }
+    }
+}
+
+int ve_k_basement(ve_ctx* ctx) {
+    unsigned nb = ve_blocks(ctx->g.n, 256);
+    k_basement<<<nb, 256, 0, ctx->stream>>>(ctx->g, ctx->max_uplift, ctx->h, ctx->b, ctx->dh, ctx->uplift, ctx->eps0,
+                                            ctx->alpha);
+    VE_LAUNCH_CHECK();
+    VE_CUDA(cudaMemcpyAsync(ctx->b_spl, ctx->b, (size_t)ctx->g.n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (ctx->max_g > 0.0f) {
+        k_lake_silt<<<nb, 256, 0, ctx->stream>>>(ctx->g, ctx->h, ctx->wh, ctx->sill_cur, ctx->lake_silt, ctx->lwv);
+        VE_LAUNCH_CHECK();
+    }
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E12 (per-cell part): effective diffusivity.  erosion.rs:1597-1611, 1627-1673.  wh already
+// holds this pass's running max (ve_g_thermal_wh), so wh[posj] is the receiver's new value.
+__global__ void __launch_bounds__(256) k_thermal_kd(Geom g, float max_uplift, double kdsed, const double* __restrict__ h,
+                                                    const double* __restrict__ b, const double* __restrict__ wh,
+                                                    const int32_t* __restrict__ dh, const double* __restrict__ kd,
+                                                    const double* __restrict__ max_slope, double* __restrict__ kd_eff) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    const double dt = (double)max_uplift / 1e-3;
+    const double sediment_thickness = 1.0e-4 * dt;
+    const double max_stable = 32.0 * 32.0 / dt;
+    double old_h_i = h[posi];
+    double sed = old_h_i - b[posi];
+    double ms = max_slope[posi];
+    double kv = (sed > sediment_thickness && kdsed > 0.0) ? kdsed : kd[posi];
+    int32_t posj = dh[posi];
+    if (posj >= 0) {
+        double wh_j = wh[posj];
+        if (wh_j < old_h_i) {
+            double h_k = h[posj];
+            double ex = (double)(g.x_of(posi) - g.x_of((uint32_t)posj)) * 32.0;
+            double ey = (double)(g.y_of(posi) - g.y_of((uint32_t)posj)) * 32.0;
+            double nd = vm_sqrt(ex * ex + ey * ey);
+            double dz = fmax(old_h_i - h_k, 0.0);
+            double mag_slope = dz / nd;
+            if (!(mag_slope >= ms)) {
+                double sr0 = mag_slope / ms;
+                double slope_ratio = sr0 * sr0;
+                double om = 1.0 - slope_ratio;
+                double f = slope_ratio * ((3.0 - slope_ratio) / (om * om));
+                kv += fmin(kv * f, max_stable);
+            }
+        }
+    }
+    kd_eff[posi] = kv;
+}
+
+int ve_k_thermal_kd(ve_ctx* ctx) {
+    double kdsed = 1.5e-2 / 4.0 * ctx->P.k_d_scale;
+    k_thermal_kd<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->max_uplift, kdsed, ctx->h, ctx->b, ctx->wh,
+                                                                    ctx->dh, ctx->kd, ctx->max_slope, ctx->kd_eff);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// E13: ADI hillslope diffusion (diffusion.rs:41-394) with the Thomas solver (408-472).
+// One thread per line keeps the reference's operation order, hence bit-exact results.
+// dir 0: x-sweep over rows 1..ny-2 (reads zp = original h for the explicit y terms, writes z).
+// dir 1: y-sweep over columns 1..nx-2 (reads z = x-sweep result, writes zp).
+__global__ void __launch_bounds__(64) k_adi_sweep(int nx, int ny, int dir, double dt, const double* __restrict__ kd,
+                                                  const double* __restrict__ src, double* __restrict__ dst,
+                                                  double* __restrict__ gam, int* __restrict__ fail) {
+    int line = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    int nlines = dir == 0 ? ny : nx;
+    if (line >= nlines - 1) return;
+    const int n = dir == 0 ? nx : ny;
+    const long long sa = dir == 0 ? 1 : nx;       // stride along the line
+    const long long sc = dir == 0 ? nx : 1;       // stride across lines
+    const long long base = (long long)line * sc;
+    const double dx = 32.0, dy = 32.0;            // xl/nx, yl/ny with xl = nx*32 (erosion.rs:1720-1721)
+    const double ca = dir == 0 ? (dx * dx) : (dy * dy); // along-line spacing^2
+    const double cc = dir == 0 ? (dy * dy) : (dx * dx); // cross-line spacing^2
+    // j = 0 : Dirichlet
+    double bet = 1.0;
+    double uprev = src[base] / bet;
+    dst[base] = uprev;
+    double prev_sup = 0.0;
+    bool bad = false;
+    for (int i = 1; i < n; ++i) {
+        long long ij = base + (long long)i * sa;
+        double inf_i, diag_i, sup_i, f_i;
+        if (i < n - 1) {
+            double kc = kd[ij];
+            double fap = (kd[ij + sa] + kc) / 2.0 * (dt / 2.0) / ca;
+            double fam = (kd[ij - sa] + kc) / 2.0 * (dt / 2.0) / ca;
+            double fcp = (kd[ij + sc] + kc) / 2.0 * (dt / 2.0) / cc;
+            double fcm = (kd[ij - sc] + kc) / 2.0 * (dt / 2.0) / cc;
+            diag_i = 1.0 + fap + fam;
+            sup_i = -fap;
+            inf_i = -fam;
+            f_i = src[ij] + fcp * src[ij + sc] - (fcp + fcm) * src[ij] + fcm * src[ij - sc];
+        } else {
+            diag_i = 1.0; inf_i = 0.0; sup_i = 0.0; f_i = src[ij];
+        }
+        double gm = prev_sup / bet;
+        gam[ij] = gm;
+        bet = diag_i - inf_i * gm;
+        if (bet == 0.0) bad = true;
+        uprev = (f_i - inf_i * uprev) / bet;
+        dst[ij] = uprev;
+        prev_sup = sup_i;
+    }
+    double unext = uprev;
+    for (int i = n - 2; i >= 0; --i) {
+        long long ij = base + (long long)i * sa;
+        double u = dst[ij];
+        u -= gam[ij + sa] * unext;
+        dst[ij] = u;
+        unext = u;
+    }
+    if (bad) *fail = 1;
+}
+
+__global__ void __launch_bounds__(256) k_adi_finish(uint32_t n, const double* __restrict__ zp, double* __restrict__ h,
+                                                    double* __restrict__ b) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double hv = zp[i];
+    h[i] = hv;
+    b[i] = fmin(hv, b[i]);
+}
+
+int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd_eff) {
+    const Geom& g = ctx->g;
+    size_t nb = (size_t)g.n * 8;
+    double *z, *zp, *gam; int* fail;
+    VE_TRY(ve_scratch(ctx, 0, nb, (void**)&z));
+    VE_TRY(ve_scratch(ctx, 1, nb, (void**)&zp));
+    VE_TRY(ve_scratch(ctx, 2, nb, (void**)&gam));
+    VE_TRY(ve_scratch(ctx, 3, 256, (void**)&fail));
+    VE_CUDA(cudaMemsetAsync(fail, 0, sizeof(int), ctx->stream));
+    // zint = h; zintp = zint.clone()  (diffusion.rs:108-120); kdsed = -1 keeps kdint = kd_eff
+    VE_CUDA(cudaMemcpyAsync(z, h, nb, cudaMemcpyDeviceToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(zp, h, nb, cudaMemcpyDeviceToDevice, ctx->stream));
+    k_adi_sweep<<<ve_blocks(g.ny, 64), 64, 0, ctx->stream>>>(g.nx, g.ny, 0, dt, kd_eff, zp, z, gam, fail);
+    VE_LAUNCH_CHECK();
+    k_adi_sweep<<<ve_blocks(g.nx, 64), 64, 0, ctx->stream>>>(g.nx, g.ny, 1, dt, kd_eff, z, zp, gam, fail);
+    VE_LAUNCH_CHECK();
+    k_adi_finish<<<ve_blocks(g.n, 256), 256, 0, ctx->stream>>>(g.n, zp, h, b);
+    VE_LAUNCH_CHECK();
+    int hfail = 0;
+    VE_CUDA(cudaMemcpyAsync(&hfail, fail, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (hfail) { ctx->err = "tridag: zero pivot"; return VE_ERR_TRIDAG_SINGULAR; }
+    return VE_OK;
+}

@@ -1,0 +1,292 @@
+"""Host side of the erosion path: a thin ctypes layer over libvelerode.so (include/velerode.h).
+
+`do_erosion` keeps the argument list and meaning of the reference's
+`world/src/sim/erosion.rs:2524-2547` (closures become callables or arrays); everything that
+computes runs in the CUDA library.  There is no CPU fallback: if the library or a CUDA device is
+missing, this module raises.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "csrc", "libvelerode.so")
+_LIB = None
+
+ARRAYS = ["h", "b", "wh", "dh", "indirection", "newh", "mrec", "mstack", "mwrec", "area", "max_slope", "kfs", "kdf",
+          "h_spl", "lake_silt", "lake_sill", "lake_water_volume", "kd_eff", "dh0", "wh_mrec", "b_spl", "h_pre_diff"]
+_DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirection=np.int32, newh=np.uint32,
+               mrec=np.uint8, mstack=np.uint32, mwrec=np.float64, area=np.float64, max_slope=np.float64,
+               kfs=np.float32, kdf=np.float32, h_spl=np.float64, lake_silt=np.float64, lake_sill=np.int32,
+               lake_water_volume=np.float64, kd_eff=np.float64, dh0=np.int32, wh_mrec=np.float64, b_spl=np.float64,
+               h_pre_diff=np.float64)
+SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater"]
+
+EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
+           "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_get_array", "ve_array_bytes",
+           "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
+           "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
+           "ve_diffusion"]
+
+
+class VeError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libvelerode error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Params(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_double) for k in ("k_d_scale", "k_da", "chunk_area_pow_q", "min_max_angle",
+                                               "max_max_angle", "mid_slope", "mountain_scale")]
+
+
+class Inputs(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_void_p) for k in ("oldh", "oldb", "is_ocean", "uplift", "n", "m", "g", "epsilon_0",
+                                               "alpha", "kf", "kd", "height_scale_cell")]
+
+
+class Noise(ctypes.Structure):
+    _fields_ = [("octaves", ctypes.c_uint32), ("frequency", ctypes.c_double), ("lacunarity", ctypes.c_double),
+                ("persistence", ctypes.c_double), ("scale_factor", ctypes.c_double), ("perm", ctypes.c_void_p)]
+
+
+PROGRESS_CB = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_double)
+
+
+def build():
+    """nvcc build for sm_100a (cross-compiles without a GPU)."""
+    subprocess.check_call(["make", "-s", "-j4", "-C", os.path.join(_HERE, "csrc")])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError("libvelerode.so is not built (run veloren_b200.erosion.build()); no CPU fallback exists")
+        L = ctypes.CDLL(_LIB_PATH)
+        L.ve_last_error.restype = ctypes.c_char_p
+        L.ve_array_bytes.restype = ctypes.c_size_t
+        L.ve_get_scalar.restype = ctypes.c_double
+        L.ve_launch_count.restype = ctypes.c_uint64
+        L.ve_timer_name.restype = ctypes.c_char_p
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class ErosionContext:
+    """Device-resident erosion state of one map (one ve_ctx)."""
+
+    def __init__(self, x_lg, y_lg, device=None):
+        L = lib()
+        self.x_lg, self.y_lg = int(x_lg), int(y_lg)
+        self.n = (1 << self.x_lg) * (1 << self.y_lg)
+        self.ctx = ctypes.c_void_p()
+        if device is None:
+            rc = L.ve_create(ctypes.byref(self.ctx), ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), None, 0)
+        else:
+            ids = (ctypes.c_int * 1)(int(device))
+            rc = L.ve_create(ctypes.byref(self.ctx), ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), ids, 1)
+        if rc != 0:
+            msg = L.ve_last_error(self.ctx).decode() if self.ctx else "ve_create failed"
+            if self.ctx:
+                L.ve_destroy(self.ctx)
+                self.ctx = None
+            raise VeError(rc, msg)
+        self._keep = []
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise VeError(rc, lib().ve_last_error(self.ctx).decode())
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            lib().ve_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- configuration -------------------------------------------------------------------------
+    def set_params(self, **kw):
+        prm = Params()
+        lib().ve_default_params(ctypes.byref(prm))
+        for k, v in kw.items():
+            setattr(prm, k, float(v))
+        self._chk(lib().ve_set_params(self.ctx, ctypes.byref(prm)))
+
+    def set_noise(self, noise):
+        perm = np.ascontiguousarray(noise["perm"], np.uint8)
+        nz = Noise(int(noise["octaves"]), float(noise["frequency"]), float(noise["lacunarity"]),
+                   float(noise["persistence"]), float(noise["scale_factor"]), _p(perm))
+        self._chk(lib().ve_set_noise(self.ctx, ctypes.byref(nz)))
+
+    def set_inputs(self, fields):
+        spec = dict(oldh=np.float32, oldb=np.float32, is_ocean=np.uint8, uplift=np.float32, n=np.float32,
+                    m=np.float32, g=np.float32, epsilon_0=np.float32, alpha=np.float32, kf=np.float64,
+                    kd=np.float64, height_scale_cell=np.float64)
+        arrs = {k: np.ascontiguousarray(fields[k], dt) for k, dt in spec.items()}
+        for k, a in arrs.items():
+            if a.size != self.n:
+                raise ValueError("%s has %d entries, expected %d" % (k, a.size, self.n))
+        inp = Inputs(*[_p(arrs[k]) for k, _ in Inputs._fields_])
+        self._chk(lib().ve_set_inputs(self.ctx, ctypes.byref(inp)))
+
+    def configure(self, fields):
+        """fields: the dict veloren_b200.synth.generate returns (arrays + scalars + noise)."""
+        self.set_params(k_d_scale=fields["k_d_scale"], k_da=fields["k_da"])
+        self.set_noise(fields["noise"])
+        self.set_inputs(fields)
+
+    def set_state(self, h=None, b=None, wh=None):
+        f = lambda a: _p(np.ascontiguousarray(a, np.float64)) if a is not None else None
+        hh, bb, ww = (np.ascontiguousarray(a, np.float64) if a is not None else None for a in (h, b, wh))
+        self._chk(lib().ve_set_state(self.ctx, _p(hh) if hh is not None else None, _p(bb) if bb is not None else None,
+                                     _p(ww) if ww is not None else None))
+
+    # -- running -------------------------------------------------------------------------------
+    def step(self):
+        self._chk(lib().ve_step(self.ctx))
+
+    def run_device(self, n_steps):
+        self._chk(lib().ve_run_device(self.ctx, ctypes.c_uint32(n_steps)))
+
+    def run(self, n_steps, report_progress=None, out_h=None, out_b=None):
+        h = out_h if out_h is not None else np.empty(self.n, np.float64)
+        b = out_b if out_b is not None else np.empty(self.n, np.float64)
+        cb = PROGRESS_CB(lambda user, pct: report_progress(pct)) if report_progress else PROGRESS_CB()
+        self._chk(lib().ve_run(self.ctx, ctypes.c_uint32(n_steps), cb, None, _p(h), _p(b)))
+        return h, b
+
+    def get(self, name):
+        which = ARRAYS.index(name)
+        nb = lib().ve_array_bytes(self.ctx, which)
+        dt = np.dtype(_DTYPES[name])
+        out = np.empty(nb // dt.itemsize, dt)
+        self._chk(lib().ve_get_array(self.ctx, which, _p(out)))
+        return out
+
+    def scalar(self, name):
+        return lib().ve_get_scalar(self.ctx, SCALARS.index(name))
+
+    def launch_count(self):
+        return int(lib().ve_launch_count(self.ctx))
+
+    def set_timing(self, on=True):
+        self._chk(lib().ve_set_timing(self.ctx, int(on)))
+
+    def timers(self):
+        buf = (ctypes.c_double * 32)()
+        n = lib().ve_get_timers(self.ctx, buf, 32)
+        return {lib().ve_timer_name(i).decode(): buf[i] for i in range(n)}
+
+    # -- post-erosion hydrology (world/src/sim/mod.rs:1474-1550) -------------------------------
+    def downhill(self, h, is_ocean):
+        h = np.ascontiguousarray(h, np.float64)
+        oc = np.ascontiguousarray(is_ocean, np.uint8)
+        dh = np.empty(self.n, np.int32)
+        self._chk(lib().ve_downhill(self.ctx, _p(h), _p(oc), _p(dh)))
+        return dh
+
+    def get_lakes(self, h, dh):
+        h = np.ascontiguousarray(h, np.float64)
+        dh = np.ascontiguousarray(dh, np.int32).copy()
+        ind = np.empty(self.n, np.int32)
+        newh = np.empty(self.n, np.uint32)
+        maxh = ctypes.c_double()
+        bl = ctypes.c_uint64()
+        self._chk(lib().ve_get_lakes(self.ctx, _p(h), _p(dh), _p(ind), _p(newh), ctypes.byref(maxh), ctypes.byref(bl)))
+        return dh, ind, newh, maxh.value, bl.value
+
+    def get_multi_rec(self, h, dh, newh, wh=None):
+        h = np.ascontiguousarray(h, np.float64)
+        dh = np.ascontiguousarray(dh, np.int32)
+        newh = np.ascontiguousarray(newh, np.uint32)
+        wh = np.zeros(self.n, np.float64) if wh is None else np.ascontiguousarray(wh, np.float64).copy()
+        mrec = np.empty(self.n, np.uint8)
+        mstack = np.empty(self.n, np.uint32)
+        mwrec = np.empty(self.n * 8, np.float64)
+        self._chk(lib().ve_get_multi_rec(self.ctx, _p(h), _p(dh), _p(newh), _p(wh), _p(mrec), _p(mstack), _p(mwrec)))
+        return wh, mrec, mstack, mwrec
+
+    def get_multi_drainage(self, mstack, mrec, mwrec):
+        area = np.empty(self.n, np.float64)
+        self._chk(lib().ve_get_multi_drainage(self.ctx, _p(np.ascontiguousarray(mstack, np.uint32)),
+                                              _p(np.ascontiguousarray(mrec, np.uint8)),
+                                              _p(np.ascontiguousarray(mwrec, np.float64)), _p(area)))
+        return area
+
+    def fill_sinks(self, h, is_ocean):
+        out = np.empty(self.n, np.float64)
+        self._chk(lib().ve_fill_sinks(self.ctx, _p(np.ascontiguousarray(h, np.float64)),
+                                      _p(np.ascontiguousarray(is_ocean, np.uint8)), _p(out)))
+        return out
+
+    def get_drainage(self, newh, dh):
+        flux = np.empty(self.n, np.float32)
+        self._chk(lib().ve_get_drainage(self.ctx, _p(np.ascontiguousarray(newh, np.uint32)),
+                                        _p(np.ascontiguousarray(dh, np.int32)), _p(flux)))
+        return flux
+
+    def diffusion(self, dt, h, b, kd):
+        h = np.ascontiguousarray(h, np.float64).copy()
+        b = np.ascontiguousarray(b, np.float64).copy()
+        self._chk(lib().ve_diffusion(self.ctx, ctypes.c_double(dt), _p(h), _p(b), _p(np.ascontiguousarray(kd, np.float64))))
+        return h, b
+
+
+def _materialise(f, n, dtype):
+    """erosion.rs:2549-2609: evaluate a per-cell closure once into a flat array."""
+    if callable(f):
+        idx = np.arange(n)
+        try:
+            out = np.asarray(f(idx))
+            if out.shape != (n,):
+                raise TypeError
+        except Exception:
+            out = np.fromiter((f(int(i)) for i in range(n)), dtype=np.float64, count=n)
+        return np.ascontiguousarray(out.astype(dtype))
+    return np.ascontiguousarray(np.asarray(f).reshape(-1).astype(dtype))
+
+
+def do_erosion(map_size_lg, _max_uplift, n_steps, seed, rock_strength_nz, oldh, oldb, is_ocean, uplift, n, theta, kf,
+               kd, g, epsilon_0, alpha, height_scale, k_d_scale, k_da_scale, threadpool=None, report_progress=None,
+               device=None):
+    """Drop-in mirror of `do_erosion` (world/src/sim/erosion.rs:2524-2547).
+
+    map_size_lg: (x_lg, y_lg).  Per-cell closures may be callables (index -> value, vectorised or
+    scalar) or arrays.  rock_strength_nz: dict with the Fbm<Perlin> tables (ve_noise_fbm_perlin3).
+    height_scale: callable n -> f64; k_da_scale: callable q -> f64.  `seed` and `threadpool` are
+    accepted and unused, as in the reference (`_seed`, erosion.rs:711).  Returns (h, b) as f64.
+    """
+    x_lg, y_lg = map_size_lg
+    N = (1 << x_lg) * (1 << y_lg)
+    n_arr = _materialise(n, N, np.float32)
+    theta_arr = _materialise(theta, N, np.float32)
+    fields = dict(
+        oldh=_materialise(oldh, N, np.float32), oldb=_materialise(oldb, N, np.float32),
+        is_ocean=_materialise(is_ocean, N, np.uint8),
+        uplift=_materialise(uplift, N, np.float64).astype(np.float32),   # `uplift(posi) as f32`, erosion.rs:2607
+        n=n_arr, m=(theta_arr * n_arr).astype(np.float32),               # f32 product, erosion.rs:2570
+        g=_materialise(g, N, np.float32), epsilon_0=_materialise(epsilon_0, N, np.float32),
+        alpha=_materialise(alpha, N, np.float32), kf=_materialise(kf, N, np.float64),
+        kd=_materialise(kd, N, np.float64),
+        height_scale_cell=np.asarray([height_scale(float(v)) for v in np.unique(n_arr)], np.float64)[
+            np.searchsorted(np.unique(n_arr), n_arr)],
+    )
+    ctx = ErosionContext(x_lg, y_lg, device=device)
+    try:
+        ctx.set_params(k_d_scale=k_d_scale, k_da=2.5 * k_da_scale(0.2))   # erosion.rs:745-750
+        ctx.set_noise(rock_strength_nz)
+        ctx.set_inputs(fields)
+        return ctx.run(n_steps, report_progress=report_progress)
+    finally:
+        ctx.close()
