@@ -1,0 +1,190 @@
+"""-m gpu: the CUDA path (through the C ABI) against the CPU oracle and the golden vectors.
+
+Bar: bit-exact for receivers, orders and lake ids; heights/flux within 1e-9 relative
+(BASELINE.json north_star) — the tests below actually require bit-identical floats too, since
+both sides evaluate the same IEEE operation sequence (include/ve_exact_math.h)."""
+import os
+
+import numpy as np
+import pytest
+
+from util import ROOT, INTERMEDIATES, INTEGER_ARRAYS, bit_diff, max_rel, compare_all, check_order_invariants
+from veloren_b200 import synth
+from veloren_b200.erosion import ErosionContext, do_erosion, VeError
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(ROOT, "tests", "golden")
+REL_TOL = 1e-9
+
+
+def _ctx(fields):
+    c = ErosionContext(fields["x_lg"], fields["y_lg"])
+    c.configure(fields)
+    return c
+
+
+def _assert_step_equal(o, c, where):
+    bad = compare_all(o, c)
+    ints = {k: v for k, v in bad.items() if k in INTEGER_ARRAYS}
+    assert not ints, "%s: integer arrays differ: %s" % (where, ints)
+    flts = {k: v for k, v in bad.items() if v[1] is not None and v[1] > REL_TOL}
+    assert not flts, "%s: floats beyond %g: %s" % (where, REL_TOL, flts)
+    assert not bad, "%s: not bit-identical (within tolerance though): %s" % (where, bad)
+    assert int(o.scalar("n_gs")) == int(c.scalar("n_gs"))
+    assert o.scalar("maxh") == c.scalar("maxh")
+    assert int(o.scalar("boundary_len")) == int(c.scalar("boundary_len"))
+
+
+@pytest.mark.parametrize("name", ["erode_fbm_32", "erode_plateau_32", "erode_fbm_64"])
+def test_gpu_matches_golden(name):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    lg, kind, steps = int(z["lg"][0]), int(z["kind"][0]), int(z["steps"][0])
+    c = _ctx(synth.generate(lg, lg, kind=kind))
+    for s in range(steps):
+        c.step()
+        for key in z.files:
+            if key.startswith("s%d_" % s) and not key.endswith("n_gs"):
+                assert bit_diff(z[key], c.get(key[len("s%d_" % s):])) == 0, key
+        assert int(z["s%d_n_gs" % s][0]) == int(c.scalar("n_gs"))
+
+
+def test_c1_256_ten_iterations_every_intermediate():
+    """configs[0]: 256x256, default seed, 10 iterations; each step starts from the oracle's state
+    and every intermediate is compared; a free-running GPU copy is compared at the end."""
+    f = synth.generate(8, 8)
+    o, c, free = po.Oracle(f), _ctx(f), _ctx(f)
+    for it in range(10):
+        c.set_state(o.get("h"), o.get("b"), o.get("wh"))
+        o.step(); c.step(); free.step()
+        _assert_step_equal(o, c, "C1 step %d" % it)
+    assert bit_diff(o.get("h"), free.get("h")) == 0 and bit_diff(o.get("b"), free.get("b")) == 0
+
+
+def test_c5_plateau_256_lake_heavy():
+    f = synth.generate(8, 8, kind=1)
+    o, c = po.Oracle(f), _ctx(f)
+    assert True
+    for it in range(4):
+        o.step(); c.step()
+        assert o.scalar("n_lakes") > 100 or it > 0
+        _assert_step_equal(o, c, "C5 step %d" % it)
+
+
+def test_non_square_and_small_maps():
+    for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
+        f = synth.generate(x_lg, y_lg)
+        o, c = po.Oracle(f), _ctx(f)
+        for it in range(2):
+            o.step(); c.step()
+            _assert_step_equal(o, c, "%dx%d step %d" % (1 << x_lg, 1 << y_lg, it))
+
+
+def test_general_exponent_and_no_deposition():
+    """n != 1 takes the general f32 powf path of the Newton loop (erosion.rs:1343-1347);
+    g == 0 everywhere makes err = 0 after one Gauss-Seidel pass (erosion.rs:1458)."""
+    f = synth.generate(6, 6)
+    f["n"] = np.full_like(f["n"], 1.25); f["m"] = (np.float32(0.4) * f["n"]).astype(np.float32)
+    o, c = po.Oracle(f), _ctx(f)
+    o.step(); c.step()
+    _assert_step_equal(o, c, "n=1.25")
+    f = synth.generate(6, 6)
+    f["g"] = np.zeros_like(f["g"])
+    o, c = po.Oracle(f), _ctx(f)
+    o.step(); c.step()
+    assert int(c.scalar("n_gs")) == 1
+    _assert_step_equal(o, c, "g=0")
+
+
+def test_default_1024_one_step_and_invariants():
+    """configs[1] size: one erode() at 1024x1024 against the oracle, plus the reference's asserts."""
+    f = synth.generate(10, 10)
+    o, c = po.Oracle(f), _ctx(f)
+    o.step(); c.step()
+    _assert_step_equal(o, c, "1024^2 step 0")
+    check_order_invariants(10, 10, c.get("dh"), c.get("newh"), c.get("mrec"), c.get("mstack"))
+    area = c.get("area")
+    assert abs(area[c.get("mrec") == 0].sum() - c.n) <= 1e-6 * c.n
+
+
+def test_do_erosion_mirror_and_progress():
+    """The do_erosion mirror (erosion.rs:2524) with closures, progress cadence (2648-2651), and
+    the zero-step call that only round-trips the state (mod.rs:1399-1421)."""
+    f = synth.generate(6, 6)
+    nz = f["noise"]
+    seen = []
+    h, b = do_erosion((6, 6), 32.0, 3, None, nz, lambda i: f["oldh"][i], f["oldb"], f["is_ocean"],
+                      lambda i: f["uplift"][i].astype(np.float64), f["n"], lambda i: np.full(np.shape(i), 0.4, np.float32),
+                      f["kf"], f["kd"], f["g"], f["epsilon_0"], f["alpha"], lambda n: 0.5 ** n, f["k_d_scale"],
+                      lambda q: 0.5 ** (-2.0 * q), report_progress=seen.append)
+    o = po.Oracle(f)
+    ho, bo = o.run(3)
+    assert seen == [(i / 3.0) * 100.0 for i in range(3)]   # (i as f64 / n_steps as f64) * 100.0
+    assert max_rel(h, ho) <= REL_TOL and max_rel(b, bo) <= REL_TOL
+    h0, b0 = do_erosion((6, 6), 1.0, 0, None, nz, h.astype(np.float32), b.astype(np.float32), f["is_ocean"], f["uplift"],
+                        f["n"], np.full(f["n"].size, 0.4, np.float32), f["kf"], f["kd"], f["g"], f["epsilon_0"], f["alpha"],
+                        lambda n: 0.5 ** n, f["k_d_scale"], lambda q: 0.5 ** (-2.0 * q))
+    assert np.array_equal(h0, h.astype(np.float32).astype(np.float64))
+
+
+def test_hydrology_entry_points():
+    """mod.rs:1474-1550: downhill (plain is_ocean predicate), get_lakes, get_multi_rec,
+    get_multi_drainage, fill_sinks, plus get_drainage and the standalone diffusion."""
+    lg = 7
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f)
+    for _ in range(2):
+        o.step()
+    alt = o.get("h")
+    oc = f["is_ocean"]
+    c = ErosionContext(lg, lg)
+    dh_o = po.downhill(lg, lg, alt, oc)
+    dh_g = c.downhill(alt, oc)
+    assert np.array_equal(dh_o, dh_g)
+    # ocean cells above zero would leave -1 lakes next to the border untouched in both paths
+    r_o = po.get_lakes(lg, lg, alt, dh_o)
+    r_g = c.get_lakes(alt, dh_g)
+    for a, b in zip(r_o[:3], r_g[:3]):
+        assert np.array_equal(a, b)
+    assert r_o[3] == r_g[3] and r_o[4] == r_g[4]
+    m_o = po.get_multi_rec(lg, lg, alt, r_o[0], r_o[2])
+    m_g = c.get_multi_rec(alt, r_g[0], r_g[2])
+    for a, b in zip(m_o, m_g):
+        assert bit_diff(a, b) == 0
+    assert bit_diff(po.get_multi_drainage(lg, lg, m_o[2], m_o[1], m_o[3]), c.get_multi_drainage(m_g[2], m_g[1], m_g[3])) == 0
+    assert bit_diff(po.get_drainage(lg, lg, r_o[2], r_o[0]), c.get_drainage(r_g[2], r_g[0])) == 0
+    w_o, _ = po.fill_sinks(lg, lg, alt, oc)
+    assert bit_diff(w_o, c.fill_sinks(alt, oc)) == 0
+    kd = o.get("kd_eff")
+    h_o, b_o = po.diffusion(1 << lg, 1 << lg, 32000.0, alt, o.get("b"), kd)
+    h_g, b_g = c.diffusion(32000.0, alt, o.get("b"), kd)
+    assert bit_diff(h_o, h_g) == 0 and bit_diff(b_o, b_g) == 0
+
+
+def test_fill_sinks_full_size_properties():
+    """1024x1024 (BASELINE size): fixed-point property instead of an oracle run."""
+    lg = 10
+    f = synth.generate(lg, lg, kind=1)
+    h = f["oldh"].astype(np.float64)
+    oc = f["is_ocean"].astype(bool)
+    c = ErosionContext(lg, lg)
+    w = c.fill_sinks(h, f["is_ocean"])
+    assert (w >= h).all() and np.array_equal(w[oc], h[oc])
+    W = w.reshape(1 << lg, 1 << lg)
+    P = np.pad(W, 1, constant_values=np.inf)
+    mn = np.full_like(W, np.inf)
+    for dy in (0, 1, 2):
+        for dx in (0, 1, 2):
+            if dy != 1 or dx != 1:
+                mn = np.minimum(mn, P[dy:dy + W.shape[0], dx:dx + W.shape[1]])
+    fixed = np.maximum(h.reshape(W.shape), mn)
+    assert np.array_equal(W[~oc.reshape(W.shape)], fixed[~oc.reshape(W.shape)])
+    assert np.array_equal(c.fill_sinks(w, f["is_ocean"]), w)   # idempotent
+
+
+def test_errors_are_reported_not_swallowed():
+    c = ErosionContext(4, 4)
+    with pytest.raises(VeError):
+        c.step()            # no inputs/noise configured
+    with pytest.raises(Exception):
+        ErosionContext(1, 1)

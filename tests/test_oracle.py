@@ -1,0 +1,138 @@
+"""CPU tests of the oracle: the reference's own asserts as invariants, analytic checks, and the
+committed golden vectors (manufactured by tests/golden/make_golden.py)."""
+import heapq
+import os
+
+import numpy as np
+import pytest
+
+from util import ROOT, check_order_invariants, bit_diff, neighbors
+from veloren_b200 import synth
+from oracle import pyoracle as po
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.mark.parametrize("name", ["erode_fbm_32", "erode_plateau_32", "erode_fbm_64"])
+def test_oracle_matches_golden(name):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    lg, kind, steps = int(z["lg"][0]), int(z["kind"][0]), int(z["steps"][0])
+    o = po.Oracle(synth.generate(lg, lg, kind=kind))
+    for s in range(steps):
+        o.step()
+        for key in z.files:
+            if key.startswith("s%d_" % s) and not key.endswith("n_gs"):
+                assert bit_diff(z[key], o.get(key[len("s%d_" % s):])) == 0, key
+        assert int(z["s%d_n_gs" % s][0]) == int(o.scalar("n_gs"))
+
+
+@pytest.mark.parametrize("lg,kind", [(6, 0), (6, 1), (7, 0)])
+def test_step_invariants(lg, kind):
+    f = synth.generate(lg, lg, kind=kind)
+    o = po.Oracle(f)
+    n = o.n
+    for _ in range(2):
+        o.step()
+        dh, newh, mrec, mstack = o.get("dh"), o.get("newh"), o.get("mrec"), o.get("mstack")
+        check_order_invariants(lg, lg, dh, newh, mrec, mstack)
+        # area conservation: every node with receivers hands on all of its area (sum w = 1)
+        area = o.get("area")
+        sinks = mrec == 0
+        assert abs(area[sinks].sum() - n) <= 1e-6 * n
+        mw = o.get("mwrec").reshape(n, 8)
+        s = mw.sum(axis=1)
+        assert np.all((np.abs(s - 1) < 1e-12) | (mrec == 0))
+        assert np.all(mw[sinks] == 0)
+        h, b = o.get("h"), o.get("b")
+        assert np.isfinite(h).all() and np.isfinite(b).all()
+        assert (b <= h).all()                                   # diffusion.rs:384-386
+        assert 1 <= o.scalar("n_gs") <= 99
+
+
+def _minimax_fill(h, ocean, x_lg, y_lg):
+    """Independent statement of fill_sinks' fixed point: W(c) = min over paths to the ocean of the
+    max height along the path (priority flood)."""
+    n = h.size
+    w = np.full(n, np.inf)
+    pq = []
+    for i in np.flatnonzero(ocean):
+        w[i] = h[i]
+        heapq.heappush(pq, (h[i], int(i)))
+    done = np.zeros(n, bool)
+    while pq:
+        lvl, i = heapq.heappop(pq)
+        if done[i]:
+            continue
+        done[i] = True
+        for j in neighbors(i, x_lg, y_lg):
+            if not ocean[j]:
+                c = max(h[j], lvl)
+                if c < w[j]:
+                    w[j] = c
+                    heapq.heappush(pq, (c, j))
+    return w
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_fill_sinks_is_the_minimax_level(kind):
+    lg = 6
+    f = synth.generate(lg, lg, kind=kind)
+    h = f["oldh"].astype(np.float64)
+    oc = f["is_ocean"]
+    out, sweeps = po.fill_sinks(lg, lg, h, oc)
+    assert sweeps >= 1
+    ref = _minimax_fill(h, oc.astype(bool), lg, lg)
+    # ocean cells are not relaxed by the reference (newh == oldh there)
+    assert bit_diff(out, np.where(oc.astype(bool), h, ref)) == 0
+    assert (out >= h).all()
+
+
+def test_diffusion_boundaries_and_residual():
+    nx = ny = 32
+    rng = np.random.default_rng(3)
+    h = rng.normal(size=nx * ny) * 10
+    b = h - rng.random(nx * ny)
+    kd = 1e-3 + rng.random(nx * ny) * 1e-2
+    dt = 32000.0
+    h2, b2 = po.diffusion(nx, ny, dt, h, b, kd)
+    H, H2 = h.reshape(ny, nx), h2.reshape(ny, nx)
+    # Dirichlet frame (diffusion.rs:177-180, 207-210, 296-299, 330-333)
+    assert np.array_equal(H[0], H2[0]) and np.array_equal(H[-1], H2[-1])
+    assert np.array_equal(H[:, 0], H2[:, 0]) and np.array_equal(H[:, -1], H2[:, -1])
+    assert (b2 <= h2).all() and (b2 <= b + 1e-300).all()
+    # diffusion smooths: interior variance does not grow
+    assert H2[1:-1, 1:-1].var() <= H[1:-1, 1:-1].var() * (1 + 1e-12)
+
+
+def test_get_drainage_counts_upstream_cells():
+    lg = 6
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f)
+    o.step()
+    dh, newh = o.get("dh"), o.get("newh")
+    flux = po.get_drainage(lg, lg, newh, dh)
+    # exact in f32 while counts stay below 2^24: flux = 1 + number of upstream cells
+    cnt = np.ones(dh.size)
+    for c in newh[::-1]:
+        if dh[c] >= 0:
+            cnt[dh[c]] += cnt[c]
+    assert np.array_equal(flux.astype(np.float64), cnt)
+    assert flux[dh < 0].sum() == dh.size
+
+
+def test_standalone_pieces_agree_with_step():
+    lg = 6
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f)
+    h0 = o.get("h").copy()
+    o.step()
+    pred = (f["is_ocean"].astype(bool) & (h0 <= 0)).astype(np.uint8)
+    dh0 = po.downhill(lg, lg, h0, pred)
+    assert np.array_equal(dh0, o.get("dh0"))
+    dh, ind, newh, maxh, bl = po.get_lakes(lg, lg, h0, dh0)
+    assert np.array_equal(dh, o.get("dh")) and np.array_equal(ind, o.get("indirection"))
+    assert np.array_equal(newh, o.get("newh")) and maxh == o.scalar("maxh") and bl == o.scalar("boundary_len")
+    wh, mrec, mstack, mwrec = po.get_multi_rec(lg, lg, h0, dh, newh)
+    assert np.array_equal(mstack, o.get("mstack")) and bit_diff(mwrec, o.get("mwrec")) == 0
+    area = po.get_multi_drainage(lg, lg, mstack, mrec, mwrec)
+    assert bit_diff(area, o.get("area")) == 0
