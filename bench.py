@@ -1,0 +1,242 @@
+#!/usr/bin/env python
+"""bench.py — erosion throughput (Mcell-iters/s) of the B200 path, per the driver's contract.
+
+  python bench.py --gpus N --steps K --warmup W            # our CUDA path
+  python bench.py --impl reference --gpus N --steps K ...   # the CPU arm (oracle on host cores)
+
+A "step" is one erode() (world/src/sim/erosion.rs:699) over the whole map.  Workload =
+BASELINE.json configs[1]: the default 1024x1024 world (MapSizeLg 10x10) with the synthetic fields
+of veloren_b200.synth (reference recipes, in-repo noise).  `value` = N_cells * K / device time,
+state resident in HBM; `e2e` = the same through the public call with host buffers (inputs H2D,
+results D2H inside the timed region).  With --gpus N>1 each rank erodes its own world (the
+reference scales the same way: world/examples/batch_generate.rs runs k independent generations);
+no data-path collective, weak scaling, value = sum over ranks / max time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+X_LG = Y_LG = 10
+# algorithmic bytes per cell of the dominant kernel (G4, the implicit up-sweep)
+G4_BYTES_PER_CELL = 145
+FIXED_BYTES_PER_CELL, GS_BYTES_PER_CELL = 684, 374
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled during the timed region (recipe's clocks line)."""
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_reference(args):
+    """CPU arm: the oracle (restatement of the reference; the reference itself is Rust and cannot be
+    built in this image) on all host cores, same config/metric.  Rank 0 only."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from veloren_b200 import synth
+    from oracle import pyoracle as po
+    fields = synth.generate(X_LG, Y_LG)
+    o = po.Oracle(fields)
+    n = o.n
+    for _ in range(args.warmup):
+        o.step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o.step()
+    dt = time.perf_counter() - t0
+    cores = os.cpu_count()
+    v = n * args.steps / dt / 1e6
+    line = {"impl": "reference", "metric": "erosion_mcell_iters_per_s", "value": v, "unit": "Mcell-iters/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(1),
+            "cpu_baseline": {"value": v, "unit": "Mcell-iters/s", "cores": cores, "kind": "port",
+                             "sample": "%d erode() steps of the 1024x1024 world after %d warm-up steps, C++ oracle "
+                                       "(OpenMP where the reference uses rayon)" % (args.steps, args.warmup)},
+            "e2e": {"value": v, "unit": "Mcell-iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus):
+    return {"workload": "default 1024x1024 world (MapSizeLg 10x10), erode() steps of the WorldSim::generate schedule",
+            "x_lg": X_LG, "y_lg": Y_LG, "seed": 130626853, "scale": 2.0,
+            "parallelism": "1 world per GPU (%d independent worlds)" % n_gpus,
+            "l2": "working set ~0.7 GB per world > 126 MB L2 (no flush needed)"}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from veloren_b200 import synth
+    from veloren_b200.erosion import ErosionContext
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # every rank erodes its own world (different seed per rank), inputs resident before timing
+    fields = synth.generate(X_LG, Y_LG, seed=130626853 + rank)
+    n = (1 << X_LG) * (1 << Y_LG)
+    ctx = ErosionContext(X_LG, Y_LG, device=local)
+    ctx.configure(fields)
+    ctx.run_device(args.warmup)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    l0 = ctx.launch_count()
+    ms = ctx.run_device_timed(args.steps)
+    launches = ctx.launch_count() - l0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = n * args.steps * world / (ms_max * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (G4 up-sweep), timed live with CUDA events ----------
+    ctx.set_timing(True)
+    up_s, n_gs_tot, gs_counts = 0.0, 0, []
+    for _ in range(2):
+        ctx.step()
+        tm = ctx.timers()
+        up_s += tm["gs_up"]
+        n_gs_tot += int(ctx.scalar("n_gs"))
+        gs_counts.append(int(ctx.scalar("n_gs")))
+    ctx.set_timing(False)
+    peak, how = peaks()
+    per_launch = up_s / max(n_gs_tot, 1)
+    achieved = G4_BYTES_PER_CELL * n / per_launch / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_dataflow<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
+                "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
+                "n_gs_per_step": gs_counts}
+
+    # ---- e2e: public call with host buffers (pinned), H2D inputs + K steps + D2H results -----
+    pinned = {}
+    for k in ("oldh", "oldb", "is_ocean", "uplift", "n", "m", "g", "epsilon_0", "alpha", "kf", "kd", "height_scale_cell"):
+        tns = torch.from_numpy(np.ascontiguousarray(fields[k])).pin_memory()
+        pinned[k] = tns.numpy()
+    out_h = torch.empty(n, dtype=torch.float64).pin_memory().numpy()
+    out_b = torch.empty(n, dtype=torch.float64).pin_memory().numpy()
+    h2d = sum(a.nbytes for a in pinned.values())
+    d2h = out_h.nbytes + out_b.nbytes
+    e2e_steps = args.steps
+    barrier()
+    t0 = time.perf_counter()
+    ctx.set_inputs(pinned)
+    ctx.run(e2e_steps, out_h=out_h, out_b=out_b)
+    torch.cuda.synchronize()
+    te = time.perf_counter() - t0
+    t = torch.tensor([te], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_v = n * e2e_steps * world / float(t.item()) / 1e6
+    e2e = {"value": e2e_v, "unit": "Mcell-iters/s", "h2d_bytes_per_step": h2d / e2e_steps, "d2h_bytes_per_step": d2h / e2e_steps,
+           "note": "ErosionContext.set_inputs + run(K) from the initial state: inputs H2D once per call, (h,b) D2H at the end",
+           "checksum_h": float(out_h.sum())}
+
+    # ---- CPU baseline on the box's host cores (rank 0, N=1 only): bounded sample ---------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import pyoracle as po
+        o = po.Oracle(fields)
+        o.step()
+        t0 = time.perf_counter()
+        cs = 3
+        for _ in range(cs):
+            o.step()
+        dt = time.perf_counter() - t0
+        cpu = {"value": n * cs / dt / 1e6, "unit": "Mcell-iters/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": "%d erode() steps (after 1 warm-up) of the same 1024x1024 world, C++ oracle, OpenMP on all host "
+                         "cores where the reference uses rayon, serial elsewhere" % cs,
+               "ms_per_step": dt / cs * 1e3}
+    if rank == 0:
+        line = {"metric": "erosion_mcell_iters_per_s", "value": value, "unit": "Mcell-iters/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": int(launches), "clocks": clocks,
+                "full_do_erosion_estimate_s": ms_max / args.steps * 100 / 1e3}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -109,6 +109,9 @@ int ve_run(ve_ctx* ctx, uint32_t n_steps, void (*progress)(void* user, double pc
 int ve_step(ve_ctx* ctx);
 /* Device-resident variant used by the benchmark: n_steps erode() calls, no host copies. */
 int ve_run_device(ve_ctx* ctx, uint32_t n_steps);
+/* Benchmark hook: ve_run_device bracketed by CUDA events recorded on the context's own stream;
+ * returns the elapsed device time in milliseconds. */
+int ve_run_device_timed(ve_ctx* ctx, uint32_t n_steps, double* elapsed_ms);
 int ve_get_array(ve_ctx* ctx, int which, void* dst);
 size_t ve_array_bytes(ve_ctx* ctx, int which);
 double ve_get_scalar(ve_ctx* ctx, int which);

@@ -257,6 +257,25 @@ int ve_run_device(ve_ctx* ctx, uint32_t n_steps) {
     return VE_OK;
 }
 
+int ve_run_device_timed(ve_ctx* ctx, uint32_t n_steps, double* elapsed_ms) {
+    if (!ctx || !elapsed_ms) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    cudaEvent_t e0, e1;
+    VE_CUDA(cudaEventCreate(&e0)); VE_CUDA(cudaEventCreate(&e1));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    VE_CUDA(cudaEventRecord(e0, ctx->stream));
+    int rc = ve_run_device(ctx, n_steps);
+    if (rc == VE_OK) {
+        VE_CUDA(cudaEventRecord(e1, ctx->stream));
+        VE_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        VE_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        *elapsed_ms = (double)ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return rc;
+}
+
 int ve_run(ve_ctx* ctx, uint32_t n_steps, void (*progress)(void* user, double pct), void* user, double* out_h, double* out_b) {
     if (!ctx) return VE_ERR_INVALID;
     for (uint32_t i = 0; i < n_steps; ++i) {

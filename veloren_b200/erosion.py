@@ -25,7 +25,7 @@ _DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirecti
 SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
-           "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_get_array", "ve_array_bytes",
+           "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion"]
@@ -158,6 +158,12 @@ class ErosionContext:
 
     def run_device(self, n_steps):
         self._chk(lib().ve_run_device(self.ctx, ctypes.c_uint32(n_steps)))
+
+    def run_device_timed(self, n_steps):
+        """n_steps erode() calls; returns device milliseconds (CUDA events on the library's stream)."""
+        ms = ctypes.c_double()
+        self._chk(lib().ve_run_device_timed(self.ctx, ctypes.c_uint32(n_steps), ctypes.byref(ms)))
+        return ms.value
 
     def run(self, n_steps, report_progress=None, out_h=None, out_b=None):
         h = out_h if out_h is not None else np.empty(self.n, np.float64)
