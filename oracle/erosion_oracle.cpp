@@ -639,6 +639,7 @@ struct orc_ctx {
     std::vector<float> kfs, kdf;
     int n_gs = 0; double err = 0, maxh = 0; uint64_t boundary_len = 0; size_t n_lakes = 0, n_sources = 0, n_underwater = 0;
     long dag_levels = -1;
+    unsigned long long newton_iters = 0, newton_nodes = 0, newton_max = 0;
     double timers[T_COUNT];
 };
 
@@ -833,6 +834,7 @@ int orc_step(orc_ctx* c) {
     }
     T[T_GATHER] = now_s() - t0;
     size_t n_underwater = 0;
+    c->newton_iters = c->newton_nodes = c->newton_max = 0;
 
     while (err > tol && n_gs < max_n_gs) {
         n_gs += 1;
@@ -935,7 +937,9 @@ int orc_step(orc_ctx* c) {
                             double h_j = h_stack[mstack_inv[pj]];
                             if (old_elev_i > h_j) { mask[kk] = true; rec_heights[kk] = (float)h_j; }
                         }
+                        c->newton_nodes++; unsigned long long nit = 0;
                         while (errp > tolp) {
+                            nit++; c->newton_iters++;
                             double f = new_h_i - h0;
                             double df = 1.0;
                             for (int kk = 0; kk < 8; ++kk) {
@@ -951,6 +955,7 @@ int orc_step(orc_ctx* c) {
                             errp = std::fabs(hn - new_h_i);
                             new_h_i = new_h_i * (1.0 - omega) + hn * omega;
                         }
+                        if (nit > c->newton_max) c->newton_max = nit;
                     }
                     lake_sill[stacki] = (int64_t)posi;
                     lake_water_volume[stacki] = 0.0;
@@ -1149,6 +1154,7 @@ double orc_get_scalar(orc_ctx* c, int which) {
         case 5: if (c->dag_levels < 0) c->dag_levels = compute_dag_levels(c); return (double)c->dag_levels;
         case 6: return (double)c->n_underwater; case 7: return (double)c->n_sources;
         case 8: return (double)c->max_uplift; case 9: return (double)c->max_g;
+        case 10: return (double)c->newton_iters; case 11: return (double)c->newton_nodes; case 12: return (double)c->newton_max;
     }
     return NAN;
 }

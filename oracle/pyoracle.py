@@ -20,7 +20,7 @@ _DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirecti
                lake_water_volume=np.float64, kd_eff=np.float64, dh0=np.int32, wh_mrec=np.float64, b_spl=np.float64,
                h_pre_diff=np.float64)
 SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "dag_levels", "n_underwater", "n_sources", "max_uplift",
-           "max_g"]
+           "max_g", "newton_iters", "newton_nodes", "newton_max"]
 
 
 class Params(ctypes.Structure):

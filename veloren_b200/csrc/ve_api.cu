@@ -3,6 +3,7 @@
 #include <math.h>
 #include <string.h>
 #include <chrono>
+#include <stdlib.h>
 
 static const char* TIMER_NAMES[VT_COUNT] = {"downhill", "get_lakes", "wh_fill", "mrec", "stack", "area", "max_slope",
                                             "k_factors", "gs_down", "gs_up", "gs_lwv", "basement", "thermal",
@@ -108,7 +109,7 @@ static int create_impl(ve_ctx* ctx, uint32_t x_lg, uint32_t y_lg, const int* dev
     VE_TRY(dev_alloc(ctx, &ctx->b_spl, n)); VE_TRY(dev_alloc(ctx, &ctx->wh_mrec, n)); VE_TRY(dev_alloc(ctx, &ctx->h_pre_diff, n));
     VE_TRY(dev_alloc(ctx, &ctx->kfs, n * 8)); VE_TRY(dev_alloc(ctx, &ctx->kdf, n * 8));
     VE_TRY(dev_alloc(ctx, &ctx->sill_cur, n)); VE_TRY(dev_alloc(ctx, &ctx->sill_prev, n));
-    VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
+    VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->order_bu, n)); VE_TRY(dev_alloc(ctx, &ctx->level, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_parent, n)); VE_TRY(dev_alloc(ctx, &ctx->f_jump, n)); VE_TRY(dev_alloc(ctx, &ctx->f_depth, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_root, n));
     VE_TRY(dev_alloc(ctx, &ctx->abort_word, 64));
@@ -128,6 +129,8 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     memset(ctx->timers, 0, sizeof(ctx->timers));
     memset(&ctx->nz, 0, sizeof(ctx->nz));
     ve_default_params(&ctx->P);
+    ctx->hop_down_ns = getenv("VE_HOP_DOWN_NS") ? (uint32_t)atoi(getenv("VE_HOP_DOWN_NS")) : 600u;
+    ctx->hop_up_ns = getenv("VE_HOP_UP_NS") ? (uint32_t)atoi(getenv("VE_HOP_UP_NS")) : 1200u;
     *out = ctx;
     return create_impl(ctx, x_lg, y_lg, device_ids, n_devices);
 }
@@ -140,7 +143,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->h, ctx->b, ctx->wh, ctx->dh, ctx->dh0, ctx->indirection, ctx->newh, ctx->mstack, ctx->stackpos,
                     ctx->mrec, ctx->ndon, ctx->mwrec, ctx->area, ctx->max_slope, ctx->kd_eff, ctx->h_t, ctx->h_new,
                     ctx->deltah, ctx->elev, ctx->h_p, ctx->lake_silt, ctx->lwv, ctx->wh_prev, ctx->h_spl, ctx->b_spl,
-                    ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td,
+                    ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td, ctx->order_bu, ctx->level,
                     ctx->don_order, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);

@@ -64,6 +64,9 @@ struct ve_ctx {
     float *kfs, *kdf;         // [cell][8]
     int32_t *sill_cur, *sill_prev;
     uint32_t *order_td;       // topological order, sources first (wh desc, stack position asc)
+    uint32_t *level;          // longest path to a sink, per node
+    uint32_t hop_down_ns, hop_up_ns; // per-level sleep estimates of the GS sweeps
+    uint32_t *order_bu;       // nodes sorted by level (longest path to a sink): sinks first
     uint32_t *don_order;      // packed donor slots sorted by stack position
     uint32_t *flags;          // dataflow completion epochs
     uint32_t epoch;

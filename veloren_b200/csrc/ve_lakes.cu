@@ -17,6 +17,8 @@
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include <string.h>
+#include <stdlib.h>
+#include <chrono>
 
 __device__ __forceinline__ int l_slot_of(int dx, int dy) { int k = (dy + 1) * 3 + (dx + 1); return k < 4 ? k : k - 1; }
 __device__ __forceinline__ uint64_t l_order_bits(double x) {
@@ -421,8 +423,21 @@ __global__ void __launch_bounds__(256) k_indirection(uint32_t n, const int32_t* 
     ind[i] = dh0[i] < 0 ? -(int32_t)(8u * size[i]) : (int32_t)root[i];   // 1891, 1900
 }
 
+struct PhaseClock {
+    bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0; const char* last;
+    PhaseClock(cudaStream_t s) : on(getenv("VE_DEBUG_LAKES") != nullptr), st(s), last(nullptr) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+    void mark(const char* name) {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[lakes] %-14s %8.3f ms\n", name, std::chrono::duration<double>(t1 - t0).count() * 1e3);
+        t0 = t1;
+    }
+};
+
 int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh) {
     const Geom& g = ctx->g;
+    PhaseClock pc(ctx->stream);
     const uint32_t n = g.n;
     const unsigned nb = ve_blocks(n, 256);
     cudaStream_t st = ctx->stream;
@@ -453,6 +468,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     VE_LAUNCH_CHECK();
     k_indirection<<<nb, 256, 0, st>>>(n, dh0, root, size, indirection);
     VE_LAUNCH_CHECK();
+    pc.mark("roots");
     // BFS keys of the dh0 forest
     uint32_t* succ; int32_t *w0, *w1; uint64_t* bfskey;
     VE_TRY(ve_scratch(ctx, 0, ((size_t)n * 2 + 64) * 4 * 2, (void**)&succ));   // sized for the final tour too
@@ -464,6 +480,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     VE_TRY(ve_list_rank(ctx, 2 * n, succ, w0, w1));
     k_bfs_key<<<nb, 256, 0, st>>>(n, w0, w1, bfskey, bad);
     VE_LAUNCH_CHECK();
+    pc.mark("bfs keys");
     // lake ranks (non-boundary roots, ascending index)
     uint32_t* flagbuf = (uint32_t*)w0; // reuse
     size_t tmp_bytes = 0; void* tmp;
@@ -499,6 +516,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_CUDA(cudaMemsetAsync(t.key, 0, (size_t)cap * 8, st));
         VE_CUDA(cudaMemsetAsync(t.hb, 0xff, (size_t)cap * 16, st)); // hb and tie = max
         for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
+        pc.mark("pass table");
         // adjacency (CSR over non-boundary lakes)
         uint32_t *deg, *off; uint64_t *adj, *ck0, *ck1, *ck0s, *ck1s;
         size_t lk = (size_t)n_lakes + 1;
@@ -530,6 +548,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
             VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0s, ck0, ck1s, ck1, (int)n_cand, 0, 64, st));
             ctx->launches += 8;
         }
+        pc.mark("adjacency");
         uint8_t* connected;
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
@@ -538,6 +557,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_CUDA(cudaMemcpyAsync(&n_flows, small + 4, 4, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
         if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
+        pc.mark("connect");
         // (v) flood: per-lake stacks carved out of one array by an exclusive scan of tree sizes
         k_save_outflow<<<ve_blocks(n_flows, 256), 256, 0, st>>>(n_flows, flows, dh, outflow);
         VE_LAUNCH_CHECK();
@@ -550,6 +570,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         k_lake_fill<<<ve_blocks(n_flows, 128), 128, 0, st>>>(g, n_flows, flows, h, root, start, dh, indirection, tag, stack, bad);
         VE_LAUNCH_CHECK();
     }
+    pc.mark("flood");
     // final order: blocks, Euler tour with virtual lake roots, ranking, stable sort by (block, depth)
     uint32_t n_blocks = n_boundary + n_flows;
     uint32_t *brank = (uint32_t*)bfskey /*scratch 4 (>= 8n bytes)*/, *block_of_root = brank + n;
@@ -589,6 +610,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
     VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_out, vals, vals_out, (int)n, 0, 64, st));
     ctx->launches += 4;
+    pc.mark("final order");
     int hbad = 0;
     VE_CUDA(cudaMemcpyAsync(&hbad, bad, 4, cudaMemcpyDeviceToHost, st));
     VE_CUDA(cudaStreamSynchronize(st));
