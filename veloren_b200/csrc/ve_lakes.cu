@@ -150,12 +150,15 @@ __global__ void __launch_bounds__(256) k_lake_flags(uint32_t n, const int32_t* _
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) fl[i] = dh0[i] == -1 ? 1u : 0u;
 }
-// adjacency degree / fill over the table; also emits the initial candidates (edges into boundary lakes)
+// adjacency degree / fill over the table; also emits the initial candidates (edges into boundary lakes).
+// Each adjacency entry carries everything the serial growth needs: (from,to) cells, the rank of
+// the lake on the other side (0xffffffff: boundary lake) and the pass-height key.
 __global__ void __launch_bounds__(256) k_adj_build(uint32_t cap, int fill, PassTable t, const int32_t* __restrict__ dh0,
                                                    const uint32_t* __restrict__ lrank, const uint32_t* __restrict__ off,
-                                                   uint32_t* __restrict__ deg, uint64_t* __restrict__ adj,
+                                                   uint32_t* __restrict__ deg, uint64_t* __restrict__ adj_ft,
+                                                   uint32_t* __restrict__ adj_tgt, uint64_t* __restrict__ adj_k0,
                                                    uint64_t* __restrict__ cand_k0, uint64_t* __restrict__ cand_k1,
-                                                   uint32_t* __restrict__ counter) {
+                                                   uint32_t* __restrict__ cand_lr, uint32_t* __restrict__ counter) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= cap || t.key[s] == 0) return;
     uint64_t pk = t.key[s] - 1ull;
@@ -165,91 +168,141 @@ __global__ void __launch_bounds__(256) k_adj_build(uint32_t cap, int fill, PassT
     bool an = dh0[A] == -1, bn = dh0[B] == -1;
     if (an) {
         uint32_t i = atomicAdd(deg + lrank[A], 1u);
-        if (fill) adj[off[lrank[A]] + i] = ((uint64_t)ca << 32) | cb;
+        if (fill) { uint32_t o = off[lrank[A]] + i; adj_ft[o] = ((uint64_t)ca << 32) | cb; adj_tgt[o] = bn ? lrank[B] : 0xffffffffu; adj_k0[o] = t.hb[s]; }
     }
     if (bn) {
         uint32_t i = atomicAdd(deg + lrank[B], 1u);
-        if (fill) adj[off[lrank[B]] + i] = ((uint64_t)cb << 32) | ca;
+        if (fill) { uint32_t o = off[lrank[B]] + i; adj_ft[o] = ((uint64_t)cb << 32) | ca; adj_tgt[o] = an ? lrank[A] : 0xffffffffu; adj_k0[o] = t.hb[s]; }
     }
     if (fill && (an != bn)) { // exactly one side is a boundary lake: 2057-2064
         uint32_t i = atomicAdd(counter, 1u);
         cand_k0[i] = t.hb[s];
         cand_k1[i] = an ? (((uint64_t)ca << 32) | cb) : (((uint64_t)cb << 32) | ca);
+        cand_lr[i] = an ? lrank[A] : lrank[B];
     }
+}
+__global__ void __launch_bounds__(256) k_lake_roots(uint32_t n, const int32_t* __restrict__ dh0, const uint32_t* __restrict__ lrank,
+                                                    uint32_t* __restrict__ lake_root) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && dh0[i] == -1) lake_root[lrank[i]] = i;
+}
+__global__ void __launch_bounds__(256) k_gather3(uint32_t n, const uint32_t* __restrict__ idx, const uint64_t* __restrict__ a0,
+                                                 const uint64_t* __restrict__ a1, const uint32_t* __restrict__ a2,
+                                                 uint64_t* __restrict__ o0, uint64_t* __restrict__ o1, uint32_t* __restrict__ o2) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t j = idx[i];
+    o0[i] = a0[j]; o1[i] = a1[j]; o2[i] = a2[j];
+}
+__global__ void __launch_bounds__(256) k_gather_u64(uint32_t n, const uint32_t* __restrict__ idx, const uint64_t* __restrict__ a,
+                                                    uint64_t* __restrict__ o) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = a[idx[i]];
+}
+__global__ void __launch_bounds__(256) k_iota32(uint32_t n, uint32_t* p) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = i;
 }
 
 // ---- (iv) Prim growth, one warp ------------------------------------------------------------------
-// 32-ary min-heap on (k0, k1); heap arrays hold `hn` entries.
+// 32-ary min-heap on (k0, k1) with payload lr (rank of the lake the candidate would connect).
+// The first HEAP_SMEM entries (levels 0..2) live in shared memory, the rest in global memory.
+#define HEAP_SMEM 1057u
 __device__ __forceinline__ bool key_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1) {
     return a0 < b0 || (a0 == b0 && a1 < b1);
 }
-__global__ void __launch_bounds__(32) k_lake_connect(const double* __restrict__ h, const int32_t* __restrict__ dh0,
-                                                     const uint32_t* __restrict__ root, const uint32_t* __restrict__ lrank,
-                                                     const uint32_t* __restrict__ off, const uint64_t* __restrict__ adj,
-                                                     uint64_t* hk0, uint64_t* hk1, uint32_t hn0, int32_t* dh,
-                                                     int32_t* indirection, uint8_t* connected, uint32_t* __restrict__ flows,
-                                                     uint32_t* __restrict__ n_flows_out) {
+struct Heap {
+    uint64_t* s0; uint64_t* s1; uint32_t* s2; uint64_t* g0; uint64_t* g1; uint32_t* g2;
+    __device__ __forceinline__ void get(uint32_t i, uint64_t& k0, uint64_t& k1, uint32_t& lr) const {
+        if (i < HEAP_SMEM) { k0 = s0[i]; k1 = s1[i]; lr = s2[i]; } else { k0 = g0[i]; k1 = g1[i]; lr = g2[i]; }
+    }
+    __device__ __forceinline__ void set(uint32_t i, uint64_t k0, uint64_t k1, uint32_t lr) const {
+        if (i < HEAP_SMEM) { s0[i] = k0; s1[i] = k1; s2[i] = lr; } else { g0[i] = k0; g1[i] = k1; g2[i] = lr; }
+    }
+};
+__global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict__ lake_root, const uint32_t* __restrict__ off,
+                                                     const uint64_t* __restrict__ adj_ft, const uint32_t* __restrict__ adj_tgt,
+                                                     const uint64_t* __restrict__ adj_k0, uint64_t* hk0, uint64_t* hk1, uint32_t* hk2,
+                                                     uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
+                                                     uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out) {
+    __shared__ uint64_t s0[HEAP_SMEM];
+    __shared__ uint64_t s1[HEAP_SMEM];
+    __shared__ uint32_t s2[HEAP_SMEM];
     const unsigned lane = threadIdx.x;
+    Heap hp{s0, s1, s2, hk0, hk1, hk2};
+    for (uint32_t i = lane; i < HEAP_SMEM && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
+    __syncwarp();
     uint32_t hn = hn0, n_flows = 0;
     while (hn > 0) {
-        // pop
-        uint64_t m1 = hk1[0];
+        uint64_t m0, m1; uint32_t mlr;
+        hp.get(0, m0, m1, mlr);
         hn--;
         if (hn > 0) {
-            uint64_t l0 = hk0[hn], l1 = hk1[hn];
+            uint64_t l0, l1; uint32_t llr;
+            hp.get(hn, l0, l1, llr);
+            __syncwarp();
             uint32_t i = 0;
             for (;;) { // sift down: the 32 children of i are scanned by the lanes
                 uint32_t c = 32u * i + 1u + lane;
-                uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t ci = c;
-                if (c < hn) { c0 = hk0[c]; c1 = hk1[c]; }
+                uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t clr = 0, ci = c;
+                if (c < hn) hp.get(c, c0, c1, clr);
                 for (int o = 16; o > 0; o >>= 1) {
                     uint64_t o0 = __shfl_xor_sync(0xffffffffu, c0, o), o1 = __shfl_xor_sync(0xffffffffu, c1, o);
-                    uint32_t oi = __shfl_xor_sync(0xffffffffu, ci, o);
-                    if (key_less(o0, o1, c0, c1) || (o0 == c0 && o1 == c1 && oi < ci)) { c0 = o0; c1 = o1; ci = oi; }
+                    uint32_t ol = __shfl_xor_sync(0xffffffffu, clr, o), oi = __shfl_xor_sync(0xffffffffu, ci, o);
+                    if (key_less(o0, o1, c0, c1) || (o0 == c0 && o1 == c1 && oi < ci)) { c0 = o0; c1 = o1; clr = ol; ci = oi; }
                 }
                 if (32u * i + 1u >= hn || !key_less(c0, c1, l0, l1)) break;
-                if (lane == 0) { hk0[i] = c0; hk1[i] = c1; }
+                if (lane == 0) hp.set(i, c0, c1, clr);
                 i = ci;
             }
-            if (lane == 0) { hk0[i] = l0; hk1[i] = l1; }
+            if (lane == 0) hp.set(i, l0, l1, llr);
             __syncwarp();
         }
+        (void)m0;
+        if (connected[mlr]) continue;                                 // 2085
         uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
-        uint32_t lake = root[from];
-        uint32_t lr = lrank[lake];
-        if (connected[lr]) continue;                                  // 2085
+        uint32_t lake = lake_root[mlr];
+        uint32_t b = off[mlr], e = off[mlr + 1];
         __syncwarp();
         if (lane == 0) {
-            connected[lr] = 1;
+            connected[mlr] = 1;
             dh[lake] = (int32_t)to;                                   // 2098
             indirection[lake] = -(int32_t)from;                       // 2103
             flows[n_flows] = lake;                                    // 2105
         }
         n_flows++;
         __syncwarp();
-        // push the reversed other passes of this lake (2107-2136)
-        uint32_t b = off[lr], e = off[lr + 1];
-        for (uint32_t a = b; a < e; ++a) {
-            uint64_t ed = adj[a];
-            uint32_t ef = (uint32_t)(ed >> 32), et = (uint32_t)ed;
-            if (ef == from && et == to) continue;
-            uint32_t tl = root[et];
-            if (dh0[tl] != -1) continue;                              // boundary lake
-            if (connected[lrank[tl]]) continue;                       // already handled
-            uint64_t k0 = l_order_bits(fmax(h[ef], h[et]));
-            uint64_t k1 = ((uint64_t)et << 32) | (uint64_t)ef;
-            if (lane == 0) { // sift up
-                uint32_t i = hn;
-                while (i > 0) {
-                    uint32_t p = (i - 1u) / 32u;
-                    if (!key_less(k0, k1, hk0[p], hk1[p])) break;
-                    hk0[i] = hk0[p]; hk1[i] = hk1[p];
-                    i = p;
-                }
-                hk0[i] = k0; hk1[i] = k1;
+        // push the reversed other passes of this lake (2107-2136); lanes evaluate edges in parallel
+        for (uint32_t a0 = b; a0 < e; a0 += 32) {
+            uint32_t a = a0 + lane;
+            uint64_t ft = 0, k0 = 0; bool ok = false;
+            if (a < e) {
+                ft = adj_ft[a]; k0 = adj_k0[a];
+                uint32_t tg = adj_tgt[a];
+                ok = (ft != m1) && (tg != 0xffffffffu) && !connected[tg];
+                // payload of the pushed candidate: the lake on the other side
+                if (ok) ft = (ft << 32) | (ft >> 32), mlr = tg;       // reversed edge (to, from)
             }
-            hn++;
-            __syncwarp();
+            unsigned bal = __ballot_sync(0xffffffffu, ok);
+            while (bal) {
+                int src = __ffs(bal) - 1; bal &= bal - 1;
+                uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
+                uint32_t plr = __shfl_sync(0xffffffffu, mlr, src);
+                if (lane == 0) { // sift up
+                    uint32_t i = hn;
+                    while (i > 0) {
+                        uint32_t pi = (i - 1u) / 32u;
+                        uint64_t q0, q1; uint32_t qlr;
+                        hp.get(pi, q0, q1, qlr);
+                        if (!key_less(p0, p1, q0, q1)) break;
+                        hp.set(i, q0, q1, qlr);
+                        i = pi;
+                    }
+                    hp.set(i, p0, p1, plr);
+                }
+                hn++;
+                __syncwarp();
+            }
         }
     }
     if (lane == 0) *n_flows_out = n_flows;
@@ -518,41 +571,58 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
         pc.mark("pass table");
         // adjacency (CSR over non-boundary lakes)
-        uint32_t *deg, *off; uint64_t *adj, *ck0, *ck1, *ck0s, *ck1s;
+        uint32_t *deg, *off, *lake_root, *adj_tgt, *cand_lr, *cand_lr_s, *cidx, *cidx2; uint64_t *adj_ft, *adj_k0, *ck0, *ck1, *ck0s, *ck1s;
         size_t lk = (size_t)n_lakes + 1;
         uint8_t* ab;
         size_t adj_cap = 2 * (size_t)n_cross + 2;
-        VE_TRY(ve_scratch(ctx, 7, lk * 8 + adj_cap * 8 * 5 + 256, (void**)&ab));
-        deg = (uint32_t*)ab; off = deg + lk;
-        adj = (uint64_t*)(ab + ((lk * 8 + 15) / 16) * 16);
-        ck0 = adj + adj_cap; ck1 = ck0 + adj_cap; ck0s = ck1 + adj_cap; ck1s = ck0s + adj_cap;
+        size_t lk16 = ((lk * 4 + 15) / 16) * 16, ac8 = adj_cap * 8, ac4 = ((adj_cap * 4 + 15) / 16) * 16;
+        VE_TRY(ve_scratch(ctx, 7, lk16 * 3 + ac8 * 6 + ac4 * 5 + 256, (void**)&ab));
+        deg = (uint32_t*)ab; off = (uint32_t*)(ab + lk16); lake_root = (uint32_t*)(ab + 2 * lk16);
+        uint8_t* q = ab + 3 * lk16;
+        adj_ft = (uint64_t*)q; q += ac8; adj_k0 = (uint64_t*)q; q += ac8; ck0 = (uint64_t*)q; q += ac8; ck1 = (uint64_t*)q; q += ac8;
+        ck0s = (uint64_t*)q; q += ac8; ck1s = (uint64_t*)q; q += ac8;
+        adj_tgt = (uint32_t*)q; q += ac4; cand_lr = (uint32_t*)q; q += ac4; cand_lr_s = (uint32_t*)q; q += ac4;
+        cidx = (uint32_t*)q; q += ac4; cidx2 = (uint32_t*)q; q += ac4;
         VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
-        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 0, t, dh0, lrank, off, deg, adj, ck0, ck1, small + 3);
+        k_lake_roots<<<nb, 256, 0, st>>>(n, dh0, lrank, lake_root);
+        VE_LAUNCH_CHECK();
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 0, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_lr, small + 3);
         VE_LAUNCH_CHECK();
         cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, deg, off, (int)lk, st);
         VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
         VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, deg, off, (int)lk, st));
         ctx->launches += 2;
         VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
-        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj, ck0, ck1, small + 3);
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_lr, small + 3);
         VE_LAUNCH_CHECK();
         uint32_t n_cand = 0;
         VE_CUDA(cudaMemcpyAsync(&n_cand, small + 3, 4, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
-        // initial heap = candidates sorted by (k0, k1): LSD passes, k1 first
-        uint64_t *h0 = ck0, *h1 = ck1;
+        // initial heap = candidates sorted by (k0, k1) (a sorted array is a valid heap): LSD, k1 first
+        uint64_t *h0 = ck0, *h1 = ck1; uint32_t* h2 = cand_lr;
         if (n_cand > 1) {
-            cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck1, ck1s, ck0, ck0s, (int)n_cand, 0, 64, st);
+            unsigned cb = ve_blocks(n_cand, 256);
+            uint64_t* keytmp = ck0s;       // sorted-key output we do not need
+            k_iota32<<<cb, 256, 0, st>>>(n_cand, cidx);
+            VE_LAUNCH_CHECK();
+            cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ck1, ck1s, cidx, cidx2, (int)n_cand, 0, 64, st);
             VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
-            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck1, ck1s, ck0, ck0s, (int)n_cand, 0, 64, st));
-            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0s, ck0, ck1s, ck1, (int)n_cand, 0, 64, st));
+            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck1, ck1s, cidx, cidx2, (int)n_cand, 0, 64, st));
+            k_gather_u64<<<cb, 256, 0, st>>>(n_cand, cidx2, ck0, ck1s);                 // k0 in k1-sorted order
+            VE_LAUNCH_CHECK();
+            VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck1s, keytmp, cidx2, cidx, (int)n_cand, 0, 64, st));
+            // cidx = permutation sorted by (k0, k1); gather the three columns into the heap arrays
+            uint64_t* g0 = ck0s; uint64_t* g1 = ck1s;
+            k_gather3<<<cb, 256, 0, st>>>(n_cand, cidx, ck0, ck1, cand_lr, g0, g1, cand_lr_s);
+            VE_LAUNCH_CHECK();
+            h0 = g0; h1 = g1; h2 = cand_lr_s;
             ctx->launches += 8;
         }
         pc.mark("adjacency");
         uint8_t* connected;
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
-        k_lake_connect<<<1, 32, 0, st>>>(h, dh0, root, lrank, off, adj, h0, h1, n_cand, dh, indirection, connected, flows, small + 4);
+        k_lake_connect<<<1, 32, 0, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, flows, small + 4);
         VE_LAUNCH_CHECK();
         VE_CUDA(cudaMemcpyAsync(&n_flows, small + 4, 4, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
