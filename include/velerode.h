@@ -135,6 +135,18 @@ int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double*
 int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux); /* erosion.rs:29-58 */
 int ve_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd);       /* diffusion.rs:41 */
 
+/* No counterpart in the reference.  Same arithmetic as ve_diffusion, for hosts that may not
+ * allocate device memory (a fixed GPU arena, or a call site where the CUDA allocator is off
+ * limits): d_h, d_b, d_kd_eff are DEVICE pointers owned by the caller (N doubles each, h and b
+ * updated in place) and the solver's work space is an array built into the library
+ * (6 MiB per GPU, held until exit), so maps are limited to 512x512 cells; larger ones return
+ * VE_ERR_TOO_LARGE with a message in errbuf.  Calls nothing that allocates.  The first call on a
+ * device looks the array's device address up: issue it before any stream capture.  All calls on a
+ * device share the array, so calls that overlap on the GPU race; serialise them.  cuda_stream: a
+ * cudaStream_t (NULL = default stream); the call returns after the work has finished. */
+int ve_diffusion_static(uint32_t x_lg, uint32_t y_lg, double dt, double* d_h, double* d_b,
+                        const double* d_kd_eff, void* cuda_stream, char* errbuf, size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

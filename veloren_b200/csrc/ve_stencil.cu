@@ -434,3 +434,96 @@ int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* k
     if (hfail) { ctx->err = "tridag: zero pivot"; return VE_ERR_TRIDAG_SINGULAR; }
     return VE_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// ve_diffusion_static — the ADI diffusion for callers that are not allowed to allocate.
+//
+// Who needs this: a host that hands this library a GPU whose memory it has already carved up
+// completely (an engine or game server running with a fixed device arena), or that calls from a
+// section of its frame where the CUDA allocator must not be entered.  Such a caller can own the
+// input/output buffers, but it cannot give us the 3 N doubles of work space the solver needs, and
+// ve_diffusion() obtains them with cudaMalloc.  Here the work space is a fixed array that is part
+// of the library image itself: every GPU that loads libvelerode.so carries these
+// VE_STATIC_SCRATCH_BYTES (6 MiB + 256 B) until the process exits, which is why the map size is
+// capped at VE_STATIC_MAX_CELLS.
+//
+// The array's name means something different on each side: device code may use it directly, host
+// code only sees a stand-in symbol, so the host asks the runtime for the real device address once
+// per device (with that device current) and passes that pointer to the kernels.  That lookup
+// happens inside the first call made on a device — make that first call outside any stream
+// capture.  All calls on a device share the one array and it keeps whatever the previous call
+// left in it; the only word that has to start at zero (the zero-pivot flag) is cleared on every
+// call, everything else is overwritten before it is read.  Two calls that overlap on the same GPU
+// (different streams, or different host threads) would trample each other's work space: serialise
+// them.
+#define VE_STATIC_MAX_CELLS (512u * 512u)
+#define VE_STATIC_SCRATCH_BYTES (3ull * VE_STATIC_MAX_CELLS * 8ull + 256ull)
+static __device__ __align__(256) unsigned char g_ve_static_scratch[VE_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+static std::mutex g_static_mu;
+static void* g_static_ptr[64];
+static bool g_static_ready[64];
+
+static void static_err(char* buf, size_t cap, const char* msg) {
+    if (buf && cap) { snprintf(buf, cap, "%s", msg); }
+}
+
+extern "C" int ve_diffusion_static(uint32_t x_lg, uint32_t y_lg, double dt, double* d_h, double* d_b, const double* d_kd_eff,
+                                   void* cuda_stream, char* errbuf, size_t errbuf_len) {
+    if (!d_h || !d_b || !d_kd_eff || x_lg < 2 || y_lg < 2 || x_lg > 14 || y_lg > 14) {
+        static_err(errbuf, errbuf_len, "ve_diffusion_static: null pointer or map size out of range");
+        return VE_ERR_INVALID;
+    }
+    const uint64_t cells = (1ull << x_lg) * (1ull << y_lg);
+    if (cells > VE_STATIC_MAX_CELLS) {
+        char m[200];
+        snprintf(m, sizeof(m), "ve_diffusion_static: %llu cells exceed the built-in work space (max %u cells = 512x512); "
+                               "use ve_diffusion, which allocates", (unsigned long long)cells, VE_STATIC_MAX_CELLS);
+        static_err(errbuf, errbuf_len, m);
+        return VE_ERR_TOO_LARGE;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) { static_err(errbuf, errbuf_len, "ve_diffusion_static: no current CUDA device"); return VE_ERR_CUDA; }
+    void* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ready[dev]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_ve_static_scratch);   // device address of the array on THIS device
+            if (e != cudaSuccess || !p) {
+                static_err(errbuf, errbuf_len, cudaGetErrorString(e));
+                return VE_ERR_CUDA;
+            }
+            g_static_ptr[dev] = p;
+            g_static_ready[dev] = true;
+        }
+        base = g_static_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int nx = 1 << x_lg, ny = 1 << y_lg;
+    const uint32_t n = (uint32_t)cells;
+    const size_t nb = (size_t)n * 8;
+    double* z = (double*)base;
+    double* zp = z + VE_STATIC_MAX_CELLS;
+    double* gam = zp + VE_STATIC_MAX_CELLS;
+    int* fail = (int*)((unsigned char*)base + 3ull * VE_STATIC_MAX_CELLS * 8ull);
+#define ST_CUDA(call)                                                                     \
+    do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { static_err(errbuf, errbuf_len, cudaGetErrorString(e_)); return VE_ERR_CUDA; } } while (0)
+    ST_CUDA(cudaMemsetAsync(fail, 0, sizeof(int), st));
+    ST_CUDA(cudaMemcpyAsync(z, d_h, nb, cudaMemcpyDeviceToDevice, st));
+    ST_CUDA(cudaMemcpyAsync(zp, d_h, nb, cudaMemcpyDeviceToDevice, st));
+    k_adi_sweep<<<ve_blocks(ny, 64), 64, 0, st>>>(nx, ny, 0, dt, d_kd_eff, zp, z, gam, fail);
+    ST_CUDA(cudaGetLastError());
+    k_adi_sweep<<<ve_blocks(nx, 64), 64, 0, st>>>(nx, ny, 1, dt, d_kd_eff, z, zp, gam, fail);
+    ST_CUDA(cudaGetLastError());
+    k_adi_finish<<<ve_blocks(n, 256), 256, 0, st>>>(n, zp, d_h, d_b);
+    ST_CUDA(cudaGetLastError());
+    int hfail = 0;
+    ST_CUDA(cudaMemcpyAsync(&hfail, fail, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ST_CUDA(cudaStreamSynchronize(st));
+#undef ST_CUDA
+    if (hfail) { static_err(errbuf, errbuf_len, "ve_diffusion_static: tridag zero pivot"); return VE_ERR_TRIDAG_SINGULAR; }
+    return VE_OK;
+}

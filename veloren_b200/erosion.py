@@ -28,7 +28,7 @@ EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_
            "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
-           "ve_diffusion"]
+           "ve_diffusion", "ve_diffusion_static"]
 
 
 class VeError(RuntimeError):
@@ -247,6 +247,18 @@ class ErosionContext:
         b = np.ascontiguousarray(b, np.float64).copy()
         self._chk(lib().ve_diffusion(self.ctx, ctypes.c_double(dt), _p(h), _p(b), _p(np.ascontiguousarray(kd, np.float64))))
         return h, b
+
+
+def diffusion_static(x_lg, y_lg, dt, d_h, d_b, d_kd_eff, stream=0):
+    """ve_diffusion_static: in-place ADI diffusion on caller-owned DEVICE buffers (integer device
+    addresses), using the work space built into the library instead of allocating.  For hosts
+    that cannot allocate GPU memory; limited to 512x512 cells.  Raises VeError otherwise."""
+    buf = ctypes.create_string_buffer(256)
+    rc = lib().ve_diffusion_static(ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), ctypes.c_double(dt),
+                                   ctypes.c_void_p(d_h), ctypes.c_void_p(d_b), ctypes.c_void_p(d_kd_eff),
+                                   ctypes.c_void_p(stream), buf, ctypes.c_size_t(256))
+    if rc != 0:
+        raise VeError(rc, buf.value.decode(errors="replace"))
 
 
 def _materialise(f, n, dtype):
