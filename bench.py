@@ -29,6 +29,8 @@ X_LG = Y_LG = 10
 # algorithmic bytes per cell of the dominant kernel (G4, the implicit up-sweep)
 G4_BYTES_PER_CELL = 145
 FIXED_BYTES_PER_CELL, GS_BYTES_PER_CELL = 684, 374
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_dataflow<OpGsUp> launch (ncu --set full, round 1)
+NCU_TRAFFIC_BYTES = 66126848 + 15436032
 
 
 def peaks():
@@ -126,7 +128,8 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # every rank erodes its own world (different seed per rank), inputs resident before timing
-    fields = synth.generate(X_LG, Y_LG, seed=130626853 + rank)
+    from veloren_b200 import multi
+    fields = synth.generate(X_LG, Y_LG, seed=multi.seed_for_rank(rank))
     n = (1 << X_LG) * (1 << Y_LG)
     ctx = ErosionContext(X_LG, Y_LG, device=local)
     ctx.configure(fields)
@@ -147,11 +150,7 @@ def run_ours(args):
     launches = ctx.launch_count() - l0
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = n * args.steps * world / (ms_max * 1e-3) / 1e6
+    value, ms_max = multi.aggregate_mcell_iters_per_s(n, args.steps, ms, device="cuda")
 
     # ---- roofline of the dominant kernel (G4 up-sweep), timed live with CUDA events ----------
     ctx.set_timing(True)
@@ -168,7 +167,7 @@ def run_ours(args):
     achieved = G4_BYTES_PER_CELL * n / per_launch / 1e9
     roofline = {"bound": "hbm", "kernel": "k_dataflow<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
                 "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
+                "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r01_ncu_full_OpGsUp.txt (dram read 66.13 MB + write 15.44 MB per launch)", "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
                 "n_gs_per_step": gs_counts}
 
     # ---- e2e: public call with host buffers (pinned), H2D inputs + K steps + D2H results -----
@@ -187,10 +186,7 @@ def run_ours(args):
     ctx.run(e2e_steps, out_h=out_h, out_b=out_b)
     torch.cuda.synchronize()
     te = time.perf_counter() - t0
-    t = torch.tensor([te], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_v = n * e2e_steps * world / float(t.item()) / 1e6
+    e2e_v, _ = multi.aggregate_mcell_iters_per_s(n, e2e_steps, te * 1e3, device="cuda")
     e2e = {"value": e2e_v, "unit": "Mcell-iters/s", "h2d_bytes_per_step": h2d / e2e_steps, "d2h_bytes_per_step": d2h / e2e_steps,
            "note": "ErosionContext.set_inputs + run(K) from the initial state: inputs H2D once per call, (h,b) D2H at the end",
            "checksum_h": float(out_h.sum())}
