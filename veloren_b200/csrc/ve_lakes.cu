@@ -224,6 +224,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                                                      const uint64_t* __restrict__ adj_ft, const uint32_t* __restrict__ adj_tgt,
                                                      const uint64_t* __restrict__ adj_k0, uint64_t* hk0, uint64_t* hk1, uint32_t* hk2,
                                                      uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
+                                                     uint64_t* best0, uint64_t* best1,
                                                      uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out) {
     __shared__ uint64_t s0[HEAP_SMEM];
     __shared__ uint64_t s1[HEAP_SMEM];
@@ -232,8 +233,14 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
     Heap hp{s0, s1, s2, hk0, hk1, hk2};
     for (uint32_t i = lane; i < HEAP_SMEM && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
     __syncwarp();
-    uint32_t hn = hn0, n_flows = 0;
+    uint32_t hn = hn0, n_flows = 0, n_pops = 0, n_push = 0;
+    // best[l] = smallest key pushed so far for lake l.  A candidate that is not smaller can never be
+    // the one that connects l (the smaller one is popped first and is never stale before l is
+    // connected), so it is not pushed at all: same result as the reference's heap, fewer heap ops.
+    // (the initial candidates are not entered into best[]: a later, worse candidate for the same lake is
+    // then pushed needlessly and popped as stale, which is harmless)
     while (hn > 0) {
+        n_pops++;
         uint64_t m0, m1; uint32_t mlr;
         hp.get(0, m0, m1, mlr);
         hn--;
@@ -281,7 +288,10 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 uint32_t tg = adj_tgt[a];
                 ok = (ft != m1) && (tg != 0xffffffffu) && !connected[tg];
                 // payload of the pushed candidate: the lake on the other side
-                if (ok) ft = (ft << 32) | (ft >> 32), mlr = tg;       // reversed edge (to, from)
+                if (ok) {
+                    ft = (ft << 32) | (ft >> 32); mlr = tg;           // reversed edge (to, from)
+                    ok = key_less(k0, ft, best0[tg], best1[tg]);      // only if it beats that lake's best so far
+                }
             }
             unsigned bal = __ballot_sync(0xffffffffu, ok);
             while (bal) {
@@ -289,6 +299,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
                 uint32_t plr = __shfl_sync(0xffffffffu, mlr, src);
                 if (lane == 0) { // sift up
+                    if (key_less(p0, p1, best0[plr], best1[plr])) { best0[plr] = p0; best1[plr] = p1; }
                     uint32_t i = hn;
                     while (i > 0) {
                         uint32_t pi = (i - 1u) / 32u;
@@ -300,12 +311,12 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                     }
                     hp.set(i, p0, p1, plr);
                 }
-                hn++;
+                hn++; n_push++;
                 __syncwarp();
             }
         }
     }
-    if (lane == 0) *n_flows_out = n_flows;
+    if (lane == 0) { *n_flows_out = n_flows; n_flows_out[1] = n_pops; n_flows_out[2] = n_push; }
 }
 
 // ---- (v) per-lake flood -----------------------------------------------------------------------------
@@ -576,13 +587,16 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         uint8_t* ab;
         size_t adj_cap = 2 * (size_t)n_cross + 2;
         size_t lk16 = ((lk * 4 + 15) / 16) * 16, ac8 = adj_cap * 8, ac4 = ((adj_cap * 4 + 15) / 16) * 16;
-        VE_TRY(ve_scratch(ctx, 7, lk16 * 3 + ac8 * 6 + ac4 * 5 + 256, (void**)&ab));
+        size_t lk8 = ((lk * 8 + 15) / 16) * 16;
+        VE_TRY(ve_scratch(ctx, 7, lk16 * 3 + ac8 * 6 + ac4 * 5 + lk8 * 2 + 256, (void**)&ab));
         deg = (uint32_t*)ab; off = (uint32_t*)(ab + lk16); lake_root = (uint32_t*)(ab + 2 * lk16);
         uint8_t* q = ab + 3 * lk16;
         adj_ft = (uint64_t*)q; q += ac8; adj_k0 = (uint64_t*)q; q += ac8; ck0 = (uint64_t*)q; q += ac8; ck1 = (uint64_t*)q; q += ac8;
         ck0s = (uint64_t*)q; q += ac8; ck1s = (uint64_t*)q; q += ac8;
         adj_tgt = (uint32_t*)q; q += ac4; cand_lr = (uint32_t*)q; q += ac4; cand_lr_s = (uint32_t*)q; q += ac4;
         cidx = (uint32_t*)q; q += ac4; cidx2 = (uint32_t*)q; q += ac4;
+        uint64_t* best0 = (uint64_t*)q; q += lk8; uint64_t* best1 = (uint64_t*)q; q += lk8;
+        VE_CUDA(cudaMemsetAsync(best0, 0xff, lk8 * 2, st));
         VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
         k_lake_roots<<<nb, 256, 0, st>>>(n, dh0, lrank, lake_root);
         VE_LAUNCH_CHECK();
@@ -622,10 +636,13 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         uint8_t* connected;
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
-        k_lake_connect<<<1, 32, 0, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, flows, small + 4);
+        k_lake_connect<<<1, 32, 0, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, best0, best1, flows, small + 12);
         VE_LAUNCH_CHECK();
-        VE_CUDA(cudaMemcpyAsync(&n_flows, small + 4, 4, cudaMemcpyDeviceToHost, st));
+        uint32_t cstat[3] = {0, 0, 0};
+        VE_CUDA(cudaMemcpyAsync(cstat, small + 12, 12, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
+        n_flows = cstat[0];
+        if (pc.on) fprintf(stderr, "[lakes] lakes %u cand %u pops %u pushes %u\n", n_lakes, n_cand, cstat[1], cstat[2]);
         if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
         pc.mark("connect");
         // (v) flood: per-lake stacks carved out of one array by an exclusive scan of tree sizes
