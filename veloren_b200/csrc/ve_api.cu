@@ -131,9 +131,13 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     ve_default_params(&ctx->P);
     ctx->hop_down_ns = getenv("VE_HOP_DOWN_NS") ? (uint32_t)atoi(getenv("VE_HOP_DOWN_NS")) : 600u;
     ctx->hop_up_ns = getenv("VE_HOP_UP_NS") ? (uint32_t)atoi(getenv("VE_HOP_UP_NS")) : 1200u;
-    ctx->lanes_down = getenv("VE_LANES_DOWN") ? (uint32_t)atoi(getenv("VE_LANES_DOWN")) : 1u;
-    ctx->lanes_up = getenv("VE_LANES_UP") ? (uint32_t)atoi(getenv("VE_LANES_UP")) : 1u;
-    ctx->lanes_other = getenv("VE_LANES_OTHER") ? (uint32_t)atoi(getenv("VE_LANES_OTHER")) : 1u;
+    // nodes per warp in the dataflow sweeps: 1 up to 4096^2 (lanes of one warp in different phases
+    // are serialised by the SIMT hardware, which stretches the critical path; measured faster at
+    // 1024^2..4096^2), 8 beyond, where node throughput of 1-node warps would bound the sweep
+    uint32_t auto_lanes = (x_lg + y_lg > 24) ? 8u : 1u;
+    ctx->lanes_down = getenv("VE_LANES_DOWN") ? (uint32_t)atoi(getenv("VE_LANES_DOWN")) : auto_lanes;
+    ctx->lanes_up = getenv("VE_LANES_UP") ? (uint32_t)atoi(getenv("VE_LANES_UP")) : auto_lanes;
+    ctx->lanes_other = getenv("VE_LANES_OTHER") ? (uint32_t)atoi(getenv("VE_LANES_OTHER")) : auto_lanes;
     *out = ctx;
     return create_impl(ctx, x_lg, y_lg, device_ids, n_devices);
 }
