@@ -207,17 +207,17 @@ __global__ void __launch_bounds__(256) k_iota32(uint32_t n, uint32_t* p) {
 // ---- (iv) Prim growth, one warp ------------------------------------------------------------------
 // 32-ary min-heap on (k0, k1) with payload lr (rank of the lake the candidate would connect).
 // The first HEAP_SMEM entries (levels 0..2) live in shared memory, the rest in global memory.
-#define HEAP_SMEM 1057u
+#define HEAP_SMEM_MAX 10240u   /* entries of 20 B: 200 KB of the 227 KB an SM offers */
 __device__ __forceinline__ bool key_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1) {
     return a0 < b0 || (a0 == b0 && a1 < b1);
 }
 struct Heap {
-    uint64_t* s0; uint64_t* s1; uint32_t* s2; uint64_t* g0; uint64_t* g1; uint32_t* g2;
+    uint64_t* s0; uint64_t* s1; uint32_t* s2; uint64_t* g0; uint64_t* g1; uint32_t* g2; uint32_t ns;
     __device__ __forceinline__ void get(uint32_t i, uint64_t& k0, uint64_t& k1, uint32_t& lr) const {
-        if (i < HEAP_SMEM) { k0 = s0[i]; k1 = s1[i]; lr = s2[i]; } else { k0 = g0[i]; k1 = g1[i]; lr = g2[i]; }
+        if (i < ns) { k0 = s0[i]; k1 = s1[i]; lr = s2[i]; } else { k0 = g0[i]; k1 = g1[i]; lr = g2[i]; }
     }
     __device__ __forceinline__ void set(uint32_t i, uint64_t k0, uint64_t k1, uint32_t lr) const {
-        if (i < HEAP_SMEM) { s0[i] = k0; s1[i] = k1; s2[i] = lr; } else { g0[i] = k0; g1[i] = k1; g2[i] = lr; }
+        if (i < ns) { s0[i] = k0; s1[i] = k1; s2[i] = lr; } else { g0[i] = k0; g1[i] = k1; g2[i] = lr; }
     }
 };
 __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict__ lake_root, const uint32_t* __restrict__ off,
@@ -225,13 +225,15 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                                                      const uint64_t* __restrict__ adj_k0, uint64_t* hk0, uint64_t* hk1, uint32_t* hk2,
                                                      uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
                                                      uint64_t* best0, uint64_t* best1,
-                                                     uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out) {
-    __shared__ uint64_t s0[HEAP_SMEM];
-    __shared__ uint64_t s1[HEAP_SMEM];
-    __shared__ uint32_t s2[HEAP_SMEM];
+                                                     uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out,
+                                                     uint32_t heap_smem) {
+    extern __shared__ __align__(16) unsigned char heap_raw[];
+    uint64_t* s0 = (uint64_t*)heap_raw;
+    uint64_t* s1 = s0 + heap_smem;
+    uint32_t* s2 = (uint32_t*)(s1 + heap_smem);
     const unsigned lane = threadIdx.x;
-    Heap hp{s0, s1, s2, hk0, hk1, hk2};
-    for (uint32_t i = lane; i < HEAP_SMEM && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
+    Heap hp{s0, s1, s2, hk0, hk1, hk2, heap_smem};
+    for (uint32_t i = lane; i < heap_smem && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
     __syncwarp();
     uint32_t hn = hn0, n_flows = 0, n_pops = 0, n_push = 0;
     // best[l] = smallest key pushed so far for lake l.  A candidate that is not smaller can never be
@@ -266,10 +268,12 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
             __syncwarp();
         }
         (void)m0;
-        if (connected[mlr]) continue;                                 // 2085
-        uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
+        // independent loads first, then the test (one round trip instead of two)
+        uint8_t already = connected[mlr];
         uint32_t lake = lake_root[mlr];
         uint32_t b = off[mlr], e = off[mlr + 1];
+        if (already) continue;                                        // 2085
+        uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
         __syncwarp();
         if (lane == 0) {
             connected[mlr] = 1;
@@ -636,7 +640,14 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         uint8_t* connected;
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
-        k_lake_connect<<<1, 32, 0, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, best0, best1, flows, small + 12);
+        {
+            // heap entries kept in shared memory: as many as can be live at once, up to 200 KB
+            uint32_t heap_smem = (uint32_t)std::min<size_t>(HEAP_SMEM_MAX, (size_t)n_cand + 2 * (size_t)n_lakes + 64);
+            size_t shb = (size_t)heap_smem * 20;
+            static bool attr_set = false;
+            if (!attr_set) { VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20))); attr_set = true; }
+            k_lake_connect<<<1, 32, shb, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, best0, best1, flows, small + 12, heap_smem);
+        }
         VE_LAUNCH_CHECK();
         uint32_t cstat[3] = {0, 0, 0};
         VE_CUDA(cudaMemcpyAsync(cstat, small + 12, 12, cudaMemcpyDeviceToHost, st));
