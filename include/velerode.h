@@ -134,6 +134,12 @@ int ve_get_multi_drainage(ve_ctx* ctx, const uint32_t* mstack, const uint8_t* mr
 int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double* out); /* erosion.rs:1738 */
 int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux); /* erosion.rs:29-58 */
 int ve_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd);       /* diffusion.rs:41 */
+/* SURVEY 8(f) rank 1 — the rest of the post-erosion hydrology wiring. */
+int ve_get_oceans(ve_ctx* ctx, const double* h, uint8_t* is_ocean);                     /* util.rs:332-367 */
+/* water_height_initial (mod.rs:1502-1543) -> fill_sinks (1550) -> final water_alt select (1566-1592).
+ * water_alt_filled (f64, may be NULL) is what get_rivers consumes; water_alt_final is the f32 field. */
+int ve_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* is_ocean, const int32_t* dh,
+                 const int32_t* indirection, double* water_alt_filled, float* water_alt_final);
 
 /* No counterpart in the reference.  Same arithmetic as ve_diffusion, for hosts that may not
  * allocate device memory (a fixed GPU arena, or a call site where the CUDA allocator is off

@@ -1191,6 +1191,53 @@ void orc_diffusion(uint32_t nx, uint32_t ny, double xl, double yl, double dt, do
                    double kdsed) {
     diffusion(nx, ny, xl, yl, dt, h, b, kd, kdsed);
 }
+// util.rs:332-367  get_oceans (stack flood fill from the border over cells with h <= 0)
+void orc_get_oceans(uint32_t x_lg, uint32_t y_lg, const double* h, uint8_t* is_ocean) {
+    Grid g = make_grid(x_lg, y_lg);
+    std::memset(is_ocean, 0, g.n);
+    std::vector<size_t> stack;
+    auto push = [&](int x, int y) { size_t p = g.idx(x, y); if (h[p] <= 0.0) stack.push_back(p); };
+    for (int x = 0; x < g.nx; ++x) { push(x, 0); push(x, g.ny - 1); }
+    for (int y = 1; y < g.ny - 1; ++y) { push(0, y); push(g.nx - 1, y); }
+    while (!stack.empty()) {
+        size_t c = stack.back(); stack.pop_back();
+        if (is_ocean[c]) continue;
+        is_ocean[c] = 1;
+        int x = g.x_of(c), y = g.y_of(c);
+        for (int k = 0; k < 8; ++k) {
+            int xx = x + NDX[k], yy = y + NDY[k];
+            if (!g.inb(xx, yy)) continue;
+            size_t p = g.idx(xx, yy);
+            if (h[p] <= 0.0) stack.push_back(p);
+        }
+    }
+}
+// mod.rs:1502-1543 water_height_initial, 1550 fill_sinks, 1566-1592 final water_alt (f32)
+void orc_water_alt(uint32_t x_lg, uint32_t y_lg, const double* alt, const uint8_t* is_ocean, const int32_t* dh,
+                   const int32_t* indirection, double* water_alt_filled, float* water_alt_final) {
+    Grid g = make_grid(x_lg, y_lg);
+    std::vector<double> init(g.n);
+    for (size_t i = 0; i < g.n; ++i) {
+        int32_t ii = indirection[i];
+        size_t lake_idx = ii < 0 ? i : (size_t)ii;
+        double chunk_water_alt;
+        if (dh[lake_idx] < 0) chunk_water_alt = 0.0;
+        else {
+            size_t pass_idx = (size_t)(-(int64_t)indirection[lake_idx]);
+            double pass_height_i = alt[pass_idx];
+            int32_t neighbor_pass_idx = dh[pass_idx];
+            double pass_height_j = alt[neighbor_pass_idx];
+            chunk_water_alt = std::max(pass_height_i, pass_height_j);
+        }
+        init[i] = std::max(alt[i], chunk_water_alt);
+    }
+    fill_sinks(g, init.data(), is_ocean, water_alt_filled);
+    for (size_t i = 0; i < g.n; ++i) {
+        int32_t ii = indirection[i];
+        size_t lake_idx = ii < 0 ? i : (size_t)ii;
+        water_alt_final[i] = dh[lake_idx] < 0 ? 0.0f : (float)water_alt_filled[i];
+    }
+}
 double orc_vm(int fn, double x, double y) {
     switch (fn) {
         case 0: return vm_log(x); case 1: return vm_exp(x); case 2: return vm_pow(x, y); case 3: return vm_log1p(x);

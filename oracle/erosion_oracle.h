@@ -83,6 +83,9 @@ int orc_fill_sinks(uint32_t x_lg, uint32_t y_lg, const double* h, const uint8_t*
                    double* out);
 void orc_diffusion(uint32_t nx, uint32_t ny, double xl, double yl, double dt, double* h,
                    double* b, const double* kd, double kdsed);
+void orc_get_oceans(uint32_t x_lg, uint32_t y_lg, const double* h, uint8_t* is_ocean);
+void orc_water_alt(uint32_t x_lg, uint32_t y_lg, const double* alt, const uint8_t* is_ocean, const int32_t* dh,
+                   const int32_t* indirection, double* water_alt_filled, float* water_alt_final);
 /* exact-math probes for tests */
 double orc_vm(int fn, double x, double y);
 

@@ -199,5 +199,20 @@ def diffusion(nx, ny, dt, h, b, kd, kdsed=-1.0):
     return h, b
 
 
+def get_oceans(x_lg, y_lg, h):
+    out = np.empty(h.size, np.uint8)
+    lib().orc_get_oceans(ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), _p(np.ascontiguousarray(h, np.float64)), _p(out))
+    return out
+
+
+def water_alt(x_lg, y_lg, alt, is_ocean, dh, indirection):
+    filled = np.empty(alt.size, np.float64)
+    final = np.empty(alt.size, np.float32)
+    lib().orc_water_alt(ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), _p(np.ascontiguousarray(alt, np.float64)),
+                        _p(np.ascontiguousarray(is_ocean, np.uint8)), _p(np.ascontiguousarray(dh, np.int32)),
+                        _p(np.ascontiguousarray(indirection, np.int32)), _p(filled), _p(final))
+    return filled, final
+
+
 def vm(fn, x, y=0.0):
     return lib().orc_vm(ctypes.c_int(fn), ctypes.c_double(x), ctypes.c_double(y))

@@ -155,6 +155,15 @@ def test_hydrology_entry_points():
     assert bit_diff(po.get_drainage(lg, lg, r_o[2], r_o[0]), c.get_drainage(r_g[2], r_g[0])) == 0
     w_o, _ = po.fill_sinks(lg, lg, alt, oc)
     assert bit_diff(w_o, c.fill_sinks(alt, oc)) == 0
+    # 8(f) rank 1: get_oceans on the eroded heights and the water_alt chain (mod.rs:1474, 1502-1592)
+    oc2_o = po.get_oceans(lg, lg, alt)
+    oc2_g = c.get_oceans(alt)
+    assert np.array_equal(oc2_o, oc2_g) and oc2_o.any()
+    dh2 = po.downhill(lg, lg, alt, oc2_o)
+    lk = po.get_lakes(lg, lg, alt, dh2)
+    f_o, w_o = po.water_alt(lg, lg, alt, oc2_o, lk[0], lk[1])
+    f_g, w_g = c.water_alt(alt, oc2_o, lk[0], lk[1])
+    assert bit_diff(f_o, f_g) == 0 and bit_diff(w_o, w_g) == 0
     kd = o.get("kd_eff")
     h_o, b_o = po.diffusion(1 << lg, 1 << lg, 32000.0, alt, o.get("b"), kd)
     h_g, b_g = c.diffusion(32000.0, alt, o.get("b"), kd)

@@ -136,3 +136,33 @@ def test_standalone_pieces_agree_with_step():
     assert np.array_equal(mstack, o.get("mstack")) and bit_diff(mwrec, o.get("mwrec")) == 0
     area = po.get_multi_drainage(lg, lg, mstack, mrec, mwrec)
     assert bit_diff(area, o.get("area")) == 0
+
+
+def test_get_oceans_is_the_border_connected_component():
+    from scipy import ndimage
+    lg = 6
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f)
+    o.step()
+    h = o.get("h")
+    oc = po.get_oceans(lg, lg, h).reshape(1 << lg, 1 << lg).astype(bool)
+    low = (h <= 0).reshape(oc.shape)
+    lab, _ = ndimage.label(low, structure=np.ones((3, 3)))
+    border = np.zeros_like(low); border[0, :] = border[-1, :] = border[:, 0] = border[:, -1] = True
+    keep = np.unique(lab[border & low])
+    assert np.array_equal(oc, np.isin(lab, keep[keep > 0]))
+
+
+def test_water_alt_properties():
+    lg = 6
+    f = synth.generate(lg, lg, kind=1)
+    o = po.Oracle(f)
+    o.step()
+    alt = o.get("h")
+    oc = po.get_oceans(lg, lg, alt)
+    dh = po.downhill(lg, lg, alt, oc)
+    dh, ind, newh, _, _ = po.get_lakes(lg, lg, alt, dh)
+    filled, final = po.water_alt(lg, lg, alt, oc, dh, ind)
+    assert (filled >= alt).all()
+    lake = np.where(ind < 0, np.arange(ind.size), ind)
+    assert (final[dh[lake] < 0] == 0).all()

@@ -447,6 +447,36 @@ int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double*
     return VE_OK;
 }
 
+int ve_get_oceans(ve_ctx* ctx, const double* h, uint8_t* is_ocean) {
+    if (!ctx || !h || !is_ocean) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    uint8_t* oc; VE_TRY(ve_scratch(ctx, 0, n, (void**)&oc));
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, h, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_get_oceans(ctx, ctx->h_t, oc));
+    VE_CUDA(cudaMemcpyAsync(is_ocean, oc, n, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* is_ocean, const int32_t* dh, const int32_t* indirection,
+                 double* water_alt_filled, float* water_alt_final) {
+    if (!ctx || !alt || !is_ocean || !dh || !indirection || !water_alt_final) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    uint8_t* oc; VE_TRY(ve_scratch(ctx, 0, n, (void**)&oc));
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, alt, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(oc, is_ocean, n, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->dh, dh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->indirection, indirection, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    float* fin = (float*)ctx->h_p;
+    VE_TRY(ve_g_water_alt(ctx, ctx->h_t, oc, ctx->dh, ctx->indirection, ctx->deltah, ctx->elev, fin));
+    if (water_alt_filled) VE_CUDA(cudaMemcpyAsync(water_alt_filled, ctx->elev, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(water_alt_final, fin, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
 int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux) {
     if (!ctx || !newh || !dh || !flux) return VE_ERR_INVALID;
     VE_CUDA(cudaSetDevice(ctx->device));

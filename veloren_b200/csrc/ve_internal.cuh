@@ -133,6 +133,9 @@ int ve_g_spl_solve(ve_ctx* ctx);            // Gauss-Seidel loop (erosion.rs:107
 int ve_g_thermal_wh(ve_ctx* ctx);           // wh running max along newh (erosion.rs:1620, 1685)
 int ve_g_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux);
 int ve_g_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* ocean, double* out);
+int ve_g_get_oceans(ve_ctx* ctx, const double* h, uint8_t* oc);
+int ve_g_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* ocean, const int32_t* dh, const int32_t* ind,
+                   double* init_scratch, double* filled, float* final_out);
 // list ranking over a forest given by successor arcs (shared by stack and lakes)
 int ve_list_rank(ve_ctx* ctx, uint32_t n_arcs, uint32_t* succ /*in, destroyed*/, int32_t* w0, int32_t* w1);
 // ve_lakes.cu

@@ -28,7 +28,7 @@ EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_
            "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
-           "ve_diffusion", "ve_diffusion_static"]
+           "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt"]
 
 
 class VeError(RuntimeError):
@@ -235,6 +235,19 @@ class ErosionContext:
         self._chk(lib().ve_fill_sinks(self.ctx, _p(np.ascontiguousarray(h, np.float64)),
                                       _p(np.ascontiguousarray(is_ocean, np.uint8)), _p(out)))
         return out
+
+    def get_oceans(self, h):
+        out = np.empty(self.n, np.uint8)
+        self._chk(lib().ve_get_oceans(self.ctx, _p(np.ascontiguousarray(h, np.float64)), _p(out)))
+        return out
+
+    def water_alt(self, alt, is_ocean, dh, indirection):
+        filled = np.empty(self.n, np.float64)
+        final = np.empty(self.n, np.float32)
+        self._chk(lib().ve_water_alt(self.ctx, _p(np.ascontiguousarray(alt, np.float64)),
+                                     _p(np.ascontiguousarray(is_ocean, np.uint8)), _p(np.ascontiguousarray(dh, np.int32)),
+                                     _p(np.ascontiguousarray(indirection, np.int32)), _p(filled), _p(final)))
+        return filled, final
 
     def get_drainage(self, newh, dh):
         flux = np.empty(self.n, np.float32)
