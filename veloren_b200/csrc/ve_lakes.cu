@@ -226,12 +226,14 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                                                      uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
                                                      uint64_t* best0, uint64_t* best1,
                                                      uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out,
-                                                     uint32_t heap_smem) {
+                                                     uint32_t heap_smem, uint32_t conn_words) {
     extern __shared__ __align__(16) unsigned char heap_raw[];
     uint64_t* s0 = (uint64_t*)heap_raw;
     uint64_t* s1 = s0 + heap_smem;
     uint32_t* s2 = (uint32_t*)(s1 + heap_smem);
+    uint32_t* cbits = s2 + heap_smem;               // "connected" bitmap (conn_words > 0), else global bytes
     const unsigned lane = threadIdx.x;
+    for (uint32_t i = lane; i < conn_words; i += 32) cbits[i] = 0u;
     Heap hp{s0, s1, s2, hk0, hk1, hk2, heap_smem};
     for (uint32_t i = lane; i < heap_smem && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
     __syncwarp();
@@ -269,14 +271,14 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
         }
         (void)m0;
         // independent loads first, then the test (one round trip instead of two)
-        uint8_t already = connected[mlr];
+        bool already = conn_words ? ((cbits[mlr >> 5] >> (mlr & 31u)) & 1u) : (connected[mlr] != 0);
         uint32_t lake = lake_root[mlr];
         uint32_t b = off[mlr], e = off[mlr + 1];
         if (already) continue;                                        // 2085
         uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
         __syncwarp();
         if (lane == 0) {
-            connected[mlr] = 1;
+            if (conn_words) cbits[mlr >> 5] |= 1u << (mlr & 31u); else connected[mlr] = 1;
             dh[lake] = (int32_t)to;                                   // 2098
             indirection[lake] = -(int32_t)from;                       // 2103
             flows[n_flows] = lake;                                    // 2105
@@ -290,7 +292,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
             if (a < e) {
                 ft = adj_ft[a]; k0 = adj_k0[a];
                 uint32_t tg = adj_tgt[a];
-                ok = (ft != m1) && (tg != 0xffffffffu) && !connected[tg];
+                ok = (ft != m1) && (tg != 0xffffffffu) && !(conn_words ? ((cbits[tg >> 5] >> (tg & 31u)) & 1u) : (uint32_t)connected[tg]);
                 // payload of the pushed candidate: the lake on the other side
                 if (ok) {
                     ft = (ft << 32) | (ft >> 32); mlr = tg;           // reversed edge (to, from)
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
                 uint32_t plr = __shfl_sync(0xffffffffu, mlr, src);
                 if (lane == 0) { // sift up
-                    if (key_less(p0, p1, best0[plr], best1[plr])) { best0[plr] = p0; best1[plr] = p1; }
+                    best0[plr] = p0; best1[plr] = p1;   // ok => this candidate beats the lake's best so far
                     uint32_t i = hn;
                     while (i > 0) {
                         uint32_t pi = (i - 1u) / 32u;
@@ -314,6 +316,94 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                         i = pi;
                     }
                     hp.set(i, p0, p1, plr);
+                }
+                hn++; n_push++;
+                __syncwarp();
+            }
+        }
+    }
+    if (lane == 0) { *n_flows_out = n_flows; n_flows_out[1] = n_pops; n_flows_out[2] = n_push; }
+}
+
+// Variant for lake graphs whose whole heap fits in shared memory (the common case after the first
+// few erosion steps): a 4-ary heap driven by lane 0 alone is several times cheaper per operation than
+// the warp-wide 32-ary heap above; the lanes still evaluate a lake's adjacency entries in parallel.
+__global__ void __launch_bounds__(32) k_lake_connect_small(const uint32_t* __restrict__ lake_root, const uint32_t* __restrict__ off,
+                                                           const uint64_t* __restrict__ adj_ft, const uint32_t* __restrict__ adj_tgt,
+                                                           const uint64_t* __restrict__ adj_k0, const uint64_t* __restrict__ hk0,
+                                                           const uint64_t* __restrict__ hk1, const uint32_t* __restrict__ hk2,
+                                                           uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
+                                                           uint64_t* best0, uint64_t* best1, uint32_t* __restrict__ flows,
+                                                           uint32_t* __restrict__ n_flows_out, uint32_t cap) {
+    extern __shared__ __align__(16) unsigned char heap_raw[];
+    uint64_t* s0 = (uint64_t*)heap_raw;
+    uint64_t* s1 = s0 + cap;
+    uint32_t* s2 = (uint32_t*)(s1 + cap);
+    const unsigned lane = threadIdx.x;
+    for (uint32_t i = lane; i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
+    __syncwarp();
+    uint32_t hn = hn0, n_flows = 0, n_pops = 0, n_push = 0;
+    while (hn > 0) {
+        n_pops++;
+        uint64_t m1 = 0; uint32_t mlr = 0;
+        if (lane == 0) {
+            m1 = s1[0]; mlr = s2[0];
+            uint32_t nh = hn - 1;
+            if (nh > 0) {
+                uint64_t l0 = s0[nh], l1 = s1[nh]; uint32_t llr = s2[nh];
+                uint32_t i = 0;
+                for (;;) {
+                    uint32_t c = 4u * i + 1u;
+                    if (c >= nh) break;
+                    uint32_t bi = c; uint64_t b0 = s0[c], b1 = s1[c];
+                    uint32_t ce = c + 4u < nh ? c + 4u : nh;
+                    for (uint32_t j = c + 1u; j < ce; ++j) { uint64_t j0 = s0[j], j1 = s1[j]; if (key_less(j0, j1, b0, b1)) { b0 = j0; b1 = j1; bi = j; } }
+                    if (!key_less(b0, b1, l0, l1)) break;
+                    s0[i] = b0; s1[i] = b1; s2[i] = s2[bi];
+                    i = bi;
+                }
+                s0[i] = l0; s1[i] = l1; s2[i] = llr;
+            }
+        }
+        hn--;
+        m1 = __shfl_sync(0xffffffffu, m1, 0); mlr = __shfl_sync(0xffffffffu, mlr, 0);
+        uint8_t already = connected[mlr];
+        uint32_t lake = lake_root[mlr];
+        uint32_t b = off[mlr], e = off[mlr + 1];
+        if (already) continue;                                        // 2085
+        uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
+        if (lane == 0) {
+            connected[mlr] = 1;
+            dh[lake] = (int32_t)to;                                   // 2098
+            indirection[lake] = -(int32_t)from;                       // 2103
+            flows[n_flows] = lake;                                    // 2105
+        }
+        n_flows++;
+        __syncwarp();
+        for (uint32_t a0 = b; a0 < e; a0 += 32) {
+            uint32_t a = a0 + lane;
+            uint64_t ft = 0, k0 = 0; uint32_t tg = 0; bool ok = false;
+            if (a < e) {
+                ft = adj_ft[a]; k0 = adj_k0[a]; tg = adj_tgt[a];
+                ok = (ft != m1) && (tg != 0xffffffffu) && !connected[tg];
+                if (ok) { ft = (ft << 32) | (ft >> 32); ok = key_less(k0, ft, best0[tg], best1[tg]); }
+            }
+            unsigned bal = __ballot_sync(0xffffffffu, ok);
+            while (bal) {
+                int src = __ffs(bal) - 1; bal &= bal - 1;
+                uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
+                uint32_t plr = __shfl_sync(0xffffffffu, tg, src);
+                if (lane == 0) {
+                    best0[plr] = p0; best1[plr] = p1;   // ok => this candidate beats the lake's best so far
+                    uint32_t i = hn;
+                    while (i > 0) {
+                        uint32_t pi = (i - 1u) >> 2;
+                        uint64_t q0 = s0[pi], q1 = s1[pi];
+                        if (!key_less(p0, p1, q0, q1)) break;
+                        s0[i] = q0; s1[i] = q1; s2[i] = s2[pi];
+                        i = pi;
+                    }
+                    s0[i] = p0; s1[i] = p1; s2[i] = plr;
                 }
                 hn++; n_push++;
                 __syncwarp();
@@ -641,12 +731,30 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
         {
-            // heap entries kept in shared memory: as many as can be live at once, up to 200 KB
-            uint32_t heap_smem = (uint32_t)std::min<size_t>(HEAP_SMEM_MAX, (size_t)n_cand + 2 * (size_t)n_lakes + 64);
-            size_t shb = (size_t)heap_smem * 20;
+            uint32_t n_adj = 0;
+            VE_CUDA(cudaMemcpyAsync(&n_adj, off + n_lakes, 4, cudaMemcpyDeviceToHost, st));
+            VE_CUDA(cudaStreamSynchronize(st));
+            size_t live_max = (size_t)n_cand + (size_t)n_adj + 8;   // every entry is pushed at most once
             static bool attr_set = false;
-            if (!attr_set) { VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20))); attr_set = true; }
-            k_lake_connect<<<1, 32, shb, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection, connected, best0, best1, flows, small + 12, heap_smem);
+            if (!attr_set) {
+                VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20)));
+                VE_CUDA(cudaFuncSetAttribute(k_lake_connect_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20)));
+                attr_set = true;
+            }
+            if (getenv("VE_FORCE_SMALL") && n_lakes < 3300) live_max = HEAP_SMEM_MAX;
+            if (live_max <= HEAP_SMEM_MAX) {
+                uint32_t cap_s = (uint32_t)live_max;
+                k_lake_connect_small<<<1, 32, (size_t)cap_s * 20, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection,
+                                                                       connected, best0, best1, flows, small + 12, cap_s);
+            } else {
+                // heap entries kept in shared memory: the top of the heap, up to 200 KB
+                // shared memory: connected bitmap first (if it fits), the top of the heap in what is left
+                uint32_t conn_words = (uint32_t)((lk + 31) / 32);
+                if ((size_t)conn_words * 4 > 96 * 1024) conn_words = 0;
+                uint32_t heap_smem = (uint32_t)((HEAP_SMEM_MAX * 20 - (size_t)conn_words * 4) / 20);
+                k_lake_connect<<<1, 32, (size_t)heap_smem * 20 + (size_t)conn_words * 4, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh,
+                                                                      indirection, connected, best0, best1, flows, small + 12, heap_smem, conn_words);
+            }
         }
         VE_LAUNCH_CHECK();
         uint32_t cstat[3] = {0, 0, 0};
