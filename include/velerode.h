@@ -141,6 +141,14 @@ int ve_get_oceans(ve_ctx* ctx, const double* h, uint8_t* is_ocean);             
 int ve_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* is_ocean, const int32_t* dh,
                  const int32_t* indirection, double* water_alt_filled, float* water_alt_final);
 
+/* SURVEY 8(f) rank 2 — get_rivers (erosion.rs:219-545).  One record per chunk mirroring RiverData
+ * (erosion.rs:153-185): kind 0 None, 1 Ocean, 2 Lake (aux = neighbor_pass_pos as two i32), 3 River
+ * (aux = cross_section as two f32).  neighbor_rivers is never filled by the reference and is omitted.
+ * newh = get_lakes' order, water_alt = ve_water_alt's filled field, drainage = ve_get_multi_drainage. */
+typedef struct { float velocity[3]; float spline_derivative[2]; int32_t kind; uint32_t aux[2]; } ve_river;
+int ve_get_rivers(ve_ctx* ctx, double continent_scale_hack, const uint32_t* newh, const double* water_alt,
+                  const int32_t* dh, const int32_t* indirection, const double* drainage, ve_river* rivers);
+
 /* No counterpart in the reference.  Same arithmetic as ve_diffusion, for hosts that may not
  * allocate device memory (a fixed GPU arena, or a call site where the CUDA allocator is off
  * limits): d_h, d_b, d_kd_eff are DEVICE pointers owned by the caller (N doubles each, h and b

@@ -1238,6 +1238,101 @@ void orc_water_alt(uint32_t x_lg, uint32_t y_lg, const double* alt, const uint8_
         water_alt_final[i] = dh[lake_idx] < 0 ? 0.0f : (float)water_alt_filled[i];
     }
 }
+// erosion.rs:219-545  get_rivers.  Output record mirrors RiverData (erosion.rs:153-185); kind: 0 None,
+// 1 Ocean, 2 Lake (aux = neighbor_pass_pos as i32 bits), 3 River (aux = cross_section).  neighbor_rivers is
+// never filled by the reference and is omitted.
+int orc_get_rivers(uint32_t x_lg, uint32_t y_lg, double continent_scale_hack, const uint32_t* newh, const double* water_alt,
+                   const int32_t* downhill_, const int32_t* indirection, const double* drainage, orc_river* rivers, int use_libm) {
+    Grid g = make_grid(x_lg, y_lg);
+    Math M; M.libm = use_libm != 0;
+    const double rainfall_chunk_rate = (double)(1.0f / (512.0f * 32.0f * 32.0f));   // config.rs:73
+    const double river_roughness = (double)0.06125f, river_max_width = (double)2.0f, river_min_height = (double)0.25f,
+                 river_width_to_depth = (double)8.0f;                                  // config.rs:74-77
+    std::memset(rivers, 0, g.n * sizeof(orc_river));
+    const double ncx = 32.0, ncy = 32.0;
+    const double mins_per_sec = 1.0 / (continent_scale_hack * continent_scale_hack);
+    const double chunk_area_factor = ncx * ncy * mins_per_sec;
+    const double derivative_divisor = 1.0;
+    for (size_t t = g.n; t-- > 0;) {
+        size_t chunk_idx = newh[t];
+        int32_t downhill_s = downhill_[chunk_idx];
+        if (downhill_s < 0) { rivers[chunk_idx].kind = 1; continue; }
+        size_t downhill_idx = (size_t)downhill_s;
+        double dx = (double)(g.x_of(downhill_idx) - g.x_of(chunk_idx)), dy = (double)(g.y_of(downhill_idx) - g.y_of(chunk_idx));
+        double ndx = ncx * dx, ndy = ncy * dy;
+        double chunk_drainage = drainage[chunk_idx];
+        double volumetric_flow_rate = chunk_drainage * chunk_area_factor * rainfall_chunk_rate;
+        double downhill_drainage = drainage[downhill_idx];
+        double incoming_drainage = downhill_drainage - 1.0;
+        // get_river_spline_derivative
+        double psx = (double)rivers[chunk_idx].spline_derivative[0], psy = (double)rivers[chunk_idx].spline_derivative[1];
+        double mdx = ndx - ncx * 2.0 * std::sqrt(2.0), mdy = ndy - ncy * 2.0 * std::sqrt(2.0);
+        double e0 = std::fabs(psx / mdx), e1 = std::fabs(psy / mdy);
+        double extra_divisor = (e0 > e1) ? e0 : e1;   // reduce_partial_max
+        float rsx, rsy;
+        if (extra_divisor > 1.0) { rsx = (float)(psx / extra_divisor); rsy = (float)(psy / extra_divisor); }
+        else { rsx = (float)psx; rsy = (float)psy; }
+        int32_t indirection_idx = indirection[chunk_idx];
+        size_t lake_idx;
+        if (indirection_idx < 0) {
+            size_t pass_idx = (size_t)(-(int64_t)indirection_idx);
+            size_t neighbor_pass_idx = (size_t)downhill_[pass_idx];
+            rivers[neighbor_pass_idx].kind = 3; rivers[neighbor_pass_idx].aux[0] = 0; rivers[neighbor_pass_idx].aux[1] = 0;
+            lake_idx = chunk_idx;
+        } else lake_idx = (size_t)indirection_idx;
+        size_t pass_idx = downhill_[lake_idx] < 0 ? lake_idx : (size_t)(-(int64_t)indirection[lake_idx]);
+        if (pass_idx != downhill_idx) {
+            double wx = (ndx * 2.0 - (double)rsx) / derivative_divisor * chunk_drainage / incoming_drainage;
+            double wy = (ndy * 2.0 - (double)rsy) / derivative_divisor * chunk_drainage / incoming_drainage;
+            rivers[downhill_idx].spline_derivative[0] += (float)wx;
+            rivers[downhill_idx].spline_derivative[1] += (float)wy;
+        }
+        int32_t neighbor_pass_s = downhill_[pass_idx];
+        double chunk_water_alt = water_alt[chunk_idx];
+        if (neighbor_pass_s >= 0) {
+            double lake_water_alt = water_alt[lake_idx];
+            if (chunk_water_alt == lake_water_alt) {
+                size_t tgt = (pass_idx == chunk_idx) ? downhill_idx : pass_idx;
+                orc_river& lake = rivers[chunk_idx];
+                lake.spline_derivative[0] = rsx; lake.spline_derivative[1] = rsy;
+                lake.kind = 2;
+                int32_t px = g.x_of(tgt) * 32, py = g.y_of(tgt) * 32;
+                std::memcpy(&lake.aux[0], &px, 4); std::memcpy(&lake.aux[1], &py, 4);
+                continue;
+            }
+        }
+        double downhill_water_alt = water_alt[downhill_idx];
+        double neighbor_distance = std::sqrt(ndx * ndx + ndy * ndy);
+        double dz = downhill_water_alt - chunk_water_alt;
+        double slope = std::fabs(dz) / neighbor_distance;
+        if (slope == 0.0) return -50; // panic!("Should this happen at all?")
+        double slope_sqrt = std::sqrt(slope);
+        double almost_velocity = volumetric_flow_rate / slope_sqrt * river_roughness;
+        double width = 5.0 * M.pow_(river_width_to_depth * M.pow_(river_width_to_depth + 2.0, 2.0 / 3.0), 3.0 / 8.0) *
+                       M.pow_(volumetric_flow_rate, 3.0 / 8.0) * M.pow_(slope, -3.0 / 16.0) * M.pow_(river_roughness, 3.0 / 8.0);
+        width = std::max(width, 0.0);
+        double height = (width == 0.0) ? river_min_height : M.pow_(almost_velocity / width, 3.0 / 5.0);
+        double sgn = dz > 0.0 ? 1.0 : (dz < 0.0 ? -1.0 : (std::signbit(dz) ? -1.0 : 1.0));
+        double rdx = ndx, rdy = ndy, rdz = sgn * dz;
+        bool is_river = rivers[chunk_idx].kind == 3 || (width >= 0.5 && height >= river_min_height);
+        if (is_river) {
+            orc_river& dr = rivers[downhill_idx];
+            dr.kind = 3; dr.aux[0] = 0; dr.aux[1] = 0;
+            double max_width = 32.0 * river_max_width;
+            if (width > max_width) { width = max_width; height = M.pow_(almost_velocity / width, 3.0 / 5.0); }
+        }
+        double velocity_magnitude = 1.0 / river_roughness * M.pow_(height, 2.0 / 3.0) * slope_sqrt;
+        float csx = (float)width, csy = (float)height;
+        double mag = std::sqrt(rdx * rdx + rdy * rdy + rdz * rdz);
+        double vx = rdx / mag * velocity_magnitude, vy = rdy / mag * velocity_magnitude, vz = rdz / mag * velocity_magnitude;
+        orc_river& r = rivers[chunk_idx];
+        r.velocity[0] = (float)vx; r.velocity[1] = (float)vy; r.velocity[2] = (float)vz;
+        r.spline_derivative[0] = rsx; r.spline_derivative[1] = rsy;
+        if (is_river) { r.kind = 3; std::memcpy(&r.aux[0], &csx, 4); std::memcpy(&r.aux[1], &csy, 4); }
+        else { r.kind = 0; r.aux[0] = 0; r.aux[1] = 0; }
+    }
+    return 0;
+}
 double orc_vm(int fn, double x, double y) {
     switch (fn) {
         case 0: return vm_log(x); case 1: return vm_exp(x); case 2: return vm_pow(x, y); case 3: return vm_log1p(x);

@@ -86,6 +86,10 @@ void orc_diffusion(uint32_t nx, uint32_t ny, double xl, double yl, double dt, do
 void orc_get_oceans(uint32_t x_lg, uint32_t y_lg, const double* h, uint8_t* is_ocean);
 void orc_water_alt(uint32_t x_lg, uint32_t y_lg, const double* alt, const uint8_t* is_ocean, const int32_t* dh,
                    const int32_t* indirection, double* water_alt_filled, float* water_alt_final);
+/* RiverData (erosion.rs:153-185) as a flat record; kind 0 None, 1 Ocean, 2 Lake, 3 River */
+typedef struct { float velocity[3]; float spline_derivative[2]; int32_t kind; uint32_t aux[2]; } orc_river;
+int orc_get_rivers(uint32_t x_lg, uint32_t y_lg, double continent_scale_hack, const uint32_t* newh, const double* water_alt,
+                   const int32_t* dh, const int32_t* indirection, const double* drainage, orc_river* rivers, int use_libm);
 /* exact-math probes for tests */
 double orc_vm(int fn, double x, double y);
 

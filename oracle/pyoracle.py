@@ -214,5 +214,20 @@ def water_alt(x_lg, y_lg, alt, is_ocean, dh, indirection):
     return filled, final
 
 
+RIVER_DTYPE = np.dtype([("velocity", np.float32, 3), ("spline_derivative", np.float32, 2), ("kind", np.int32),
+                        ("aux", np.uint32, 2)])
+
+
+def get_rivers(x_lg, y_lg, scale, newh, water_alt_filled, dh, indirection, drainage, use_libm=False):
+    out = np.zeros(dh.size, RIVER_DTYPE)
+    rc = lib().orc_get_rivers(ctypes.c_uint32(x_lg), ctypes.c_uint32(y_lg), ctypes.c_double(scale),
+                              _p(np.ascontiguousarray(newh, np.uint32)), _p(np.ascontiguousarray(water_alt_filled, np.float64)),
+                              _p(np.ascontiguousarray(dh, np.int32)), _p(np.ascontiguousarray(indirection, np.int32)),
+                              _p(np.ascontiguousarray(drainage, np.float64)), _p(out), ctypes.c_int(int(use_libm)))
+    if rc != 0:
+        raise RuntimeError("oracle get_rivers failed: %d" % rc)
+    return out
+
+
 def vm(fn, x, y=0.0):
     return lib().orc_vm(ctypes.c_int(fn), ctypes.c_double(x), ctypes.c_double(y))

@@ -164,6 +164,13 @@ def test_hydrology_entry_points():
     f_o, w_o = po.water_alt(lg, lg, alt, oc2_o, lk[0], lk[1])
     f_g, w_g = c.water_alt(alt, oc2_o, lk[0], lk[1])
     assert bit_diff(f_o, f_g) == 0 and bit_diff(w_o, w_g) == 0
+    # 8(f) rank 2: get_rivers on the same fields (mod.rs:1556-1564)
+    mr = po.get_multi_rec(lg, lg, alt, lk[0], lk[2])
+    fl = po.get_multi_drainage(lg, lg, mr[2], mr[1], mr[3])
+    r_o = po.get_rivers(lg, lg, 2.0, lk[2], f_o, lk[0], lk[1], fl)
+    r_g = c.get_rivers(2.0, lk[2], f_o, lk[0], lk[1], fl)
+    assert r_o.tobytes() == r_g.tobytes()
+    assert (r_o["kind"] == 3).any() and (r_o["kind"] == 1).any()
     kd = o.get("kd_eff")
     h_o, b_o = po.diffusion(1 << lg, 1 << lg, 32000.0, alt, o.get("b"), kd)
     h_g, b_g = c.diffusion(32000.0, alt, o.get("b"), kd)

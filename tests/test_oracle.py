@@ -166,3 +166,28 @@ def test_water_alt_properties():
     assert (filled >= alt).all()
     lake = np.where(ind < 0, np.arange(ind.size), ind)
     assert (final[dh[lake] < 0] == 0).all()
+
+
+def test_get_rivers_invariants():
+    lg = 7
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f)
+    for _ in range(3):
+        o.step()
+    alt = o.get("h")
+    oc = po.get_oceans(lg, lg, alt)
+    dh = po.downhill(lg, lg, alt, oc)
+    dh, ind, newh, _, _ = po.get_lakes(lg, lg, alt, dh)
+    wh, mrec, mstack, mwrec = po.get_multi_rec(lg, lg, alt, dh, newh)
+    area = po.get_multi_drainage(lg, lg, mstack, mrec, mwrec)
+    filled, _ = po.water_alt(lg, lg, alt, oc, dh, ind)
+    r = po.get_rivers(lg, lg, 2.0, newh, filled, dh, ind, area)
+    kind = r["kind"]
+    assert ((kind == 1) == (dh < 0)).all()                     # ocean <=> no receiver (erosion.rs:253-258)
+    riv = np.flatnonzero(kind == 3)
+    assert riv.size > 0
+    # "unbroken stream": a river's receiver is a river, a lake or the ocean (erosion.rs:489-493)
+    assert (kind[dh[riv]] != 0).all()
+    cs = r["aux"][riv].view(np.float32)
+    assert (cs[:, 0] <= 64.0 + 1e-6).all()                     # width capped at RECT_SIZE.x * river_max_width
+    assert np.isfinite(r["velocity"]).all() and np.isfinite(r["spline_derivative"]).all()

@@ -477,6 +477,23 @@ int ve_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* is_ocean, const 
     return VE_OK;
 }
 
+int ve_get_rivers(ve_ctx* ctx, double continent_scale_hack, const uint32_t* newh, const double* water_alt, const int32_t* dh,
+                  const int32_t* indirection, const double* drainage, ve_river* rivers) {
+    if (!ctx || !newh || !water_alt || !dh || !indirection || !drainage || !rivers) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    VE_CUDA(cudaMemcpyAsync(ctx->newh, newh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->h_t, water_alt, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->dh, dh, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->indirection, indirection, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->area, drainage, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    void* out = (void*)ctx->mwrec;   // 64 B per cell available, 32 needed
+    VE_TRY(ve_g_get_rivers(ctx, continent_scale_hack, ctx->newh, ctx->h_t, ctx->dh, ctx->indirection, ctx->area, out));
+    VE_CUDA(cudaMemcpyAsync(rivers, out, n * sizeof(ve_river), cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
 int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux) {
     if (!ctx || !newh || !dh || !flux) return VE_ERR_INVALID;
     VE_CUDA(cudaSetDevice(ctx->device));

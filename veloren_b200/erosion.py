@@ -28,7 +28,7 @@ EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_
            "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
-           "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt"]
+           "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers"]
 
 
 class VeError(RuntimeError):
@@ -51,6 +51,9 @@ class Noise(ctypes.Structure):
     _fields_ = [("octaves", ctypes.c_uint32), ("frequency", ctypes.c_double), ("lacunarity", ctypes.c_double),
                 ("persistence", ctypes.c_double), ("scale_factor", ctypes.c_double), ("perm", ctypes.c_void_p)]
 
+
+RIVER_DTYPE = np.dtype([("velocity", np.float32, 3), ("spline_derivative", np.float32, 2), ("kind", np.int32),
+                        ("aux", np.uint32, 2)])   # ve_river
 
 PROGRESS_CB = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_double)
 
@@ -248,6 +251,14 @@ class ErosionContext:
                                      _p(np.ascontiguousarray(is_ocean, np.uint8)), _p(np.ascontiguousarray(dh, np.int32)),
                                      _p(np.ascontiguousarray(indirection, np.int32)), _p(filled), _p(final)))
         return filled, final
+
+    def get_rivers(self, scale, newh, water_alt_filled, dh, indirection, drainage):
+        out = np.zeros(self.n, RIVER_DTYPE)
+        self._chk(lib().ve_get_rivers(self.ctx, ctypes.c_double(scale), _p(np.ascontiguousarray(newh, np.uint32)),
+                                      _p(np.ascontiguousarray(water_alt_filled, np.float64)),
+                                      _p(np.ascontiguousarray(dh, np.int32)), _p(np.ascontiguousarray(indirection, np.int32)),
+                                      _p(np.ascontiguousarray(drainage, np.float64)), _p(out)))
+        return out
 
     def get_drainage(self, newh, dh):
         flux = np.empty(self.n, np.float32)
