@@ -149,6 +149,15 @@ typedef struct { float velocity[3]; float spline_derivative[2]; int32_t kind; ui
 int ve_get_rivers(ve_ctx* ctx, double continent_scale_hack, const uint32_t* newh, const double* water_alt,
                   const int32_t* dh, const int32_t* indirection, const double* drainage, ve_river* rivers);
 
+/* SURVEY 8(f) rank 3/4 — pre- and post-processing around the path.
+ * uniform_noise (util.rs:171-207): values[i] = the sample, NaN = None; cdf[i] = (1 + rank) / count as f32
+ * with ties broken by index, 0 for None. */
+int ve_uniform_noise(ve_ctx* ctx, const float* values, float* cdf);
+/* get_horizon_map (util.rs:371-449) for bounds = the whole map, F = f32: raw slope ("angle" before
+ * to_angle) and occluder height (before to_height) for the west and the east march. */
+int ve_horizon_map(ve_ctx* ctx, float minh, float maxh, const float* h, float* west_angle, float* west_height,
+                   float* east_angle, float* east_height);
+
 /* No counterpart in the reference.  Same arithmetic as ve_diffusion, for hosts that may not
  * allocate device memory (a fixed GPU arena, or a call site where the CUDA allocator is off
  * limits): d_h, d_b, d_kd_eff are DEVICE pointers owned by the caller (N doubles each, h and b

@@ -229,5 +229,46 @@ def get_rivers(x_lg, y_lg, scale, newh, water_alt_filled, dh, indirection, drain
     return out
 
 
+def uniform_noise(values):
+    """util.rs:171-207 restated in numpy: NaN = None; (1 + rank) as f32 / count as f32, ties by index."""
+    v = np.asarray(values, np.float32)
+    out = np.zeros(v.size, np.float32)
+    idx = np.flatnonzero(~np.isnan(v))
+    order = idx[np.lexsort((idx, v[idx]))]
+    total = np.float32(order.size)
+    out[order] = (np.arange(1, order.size + 1).astype(np.float32)) / total
+    return out
+
+
+def horizon_map(x_lg, y_lg, minh, maxh, h):
+    """util.rs:371-449 restated literally (pure Python loops: small maps only), F = f32."""
+    nx, ny = 1 << x_lg, 1 << y_lg
+    h = np.asarray(h, np.float32)
+    f = np.float32
+    res = []
+    for step in (-1, 1):
+        ang = np.zeros(h.size, np.float32); hei = np.zeros(h.size, np.float32)
+        for posi in range(h.size):
+            x = posi & (nx - 1)
+            maxdx = x if step < 0 else nx - x
+            slope = f(0); h0 = h[posi]
+            if h0 < f(minh):
+                hv = f(0)
+            else:
+                max_height = f(0); maxdz = f(maxh) - h0
+                for d in range(1, maxdx):
+                    deltax = f(32) * f(d)
+                    est = slope * deltax
+                    if est > maxdz:
+                        break
+                    act = h[posi + d * step] - h0
+                    if est <= act:
+                        slope = act / deltax; max_height = act
+                hv = h0 - f(minh) + max_height
+            ang[posi] = slope; hei[posi] = hv
+        res += [ang, hei]
+    return res
+
+
 def vm(fn, x, y=0.0):
     return lib().orc_vm(ctypes.c_int(fn), ctypes.c_double(x), ctypes.c_double(y))

@@ -204,3 +204,21 @@ def test_errors_are_reported_not_swallowed():
         c.step()            # no inputs/noise configured
     with pytest.raises(Exception):
         ErosionContext(1, 1)
+
+
+def test_uniform_noise_and_horizon_map():
+    """rank CDF (util.rs:171-207) and the horizon ray march (util.rs:371-449)."""
+    lg = 6
+    f = synth.generate(lg, lg)
+    c = ErosionContext(lg, lg)
+    v = f["oldh"].astype(np.float32).copy()
+    v[f["is_ocean"].astype(bool)] = np.nan          # None on ocean chunks, as at mod.rs:1118-1124
+    v[5:50] = v[5]                                  # ties -> broken by index
+    assert bit_diff(po.uniform_noise(v), c.uniform_noise(v)) == 0
+    h = (f["oldh"].astype(np.float32) * np.float32(0.25) + np.float32(140.0))
+    got = c.horizon_map(140.0, 140.0 + 300.0, h)
+    want = po.horizon_map(lg, lg, 140.0, 140.0 + 300.0, h)
+    for a, b in zip(want, got):
+        assert bit_diff(a, b) == 0
+    with pytest.raises(VeError):
+        c.horizon_map(10.0, 5.0, h)

@@ -191,3 +191,31 @@ def test_get_rivers_invariants():
     cs = r["aux"][riv].view(np.float32)
     assert (cs[:, 0] <= 64.0 + 1e-6).all()                     # width capped at RECT_SIZE.x * river_max_width
     assert np.isfinite(r["velocity"]).all() and np.isfinite(r["spline_derivative"]).all()
+
+
+def test_world_file_codec_round_trip(tmp_path):
+    """bincode-legacy layout of WorldFile::Veloren0_7_0 (mod.rs:498-551)."""
+    import struct
+    from veloren_b200 import worldfile
+    n = 16 * 8
+    alt = np.arange(n, dtype=np.float64) * 0.5 - 3
+    bas = alt - 1.25
+    p = tmp_path / "map.bin"
+    worldfile.save(p, alt, bas, 4, 3, 2.157574498096227)
+    raw = p.read_bytes()
+    assert len(raw) == 4 + 8 + 8 + 8 + n * 8 + 8 + n * 8
+    assert struct.unpack_from("<IIIdQ", raw, 0) == (1, 4, 3, 2.157574498096227, n)
+    m = worldfile.load(p)
+    assert m["version"] == "0.7.0" and (m["x_lg"], m["y_lg"]) == (4, 3)
+    assert np.array_equal(m["alt"], alt) and np.array_equal(m["basement"], bas)
+    # a 0.5.0 file: variant 0, no size header
+    p2 = tmp_path / "old.bin"
+    p2.write_bytes(struct.pack("<IQ", 0, 2) + np.array([1.0, 2.0]).tobytes() + struct.pack("<Q", 2) + np.array([0.5, 1.5]).tobytes())
+    m2 = worldfile.load(p2)
+    assert m2["version"] == "0.5.0" and np.array_equal(m2["basement"], [0.5, 1.5])
+
+
+def test_uniform_noise_restated():
+    v = np.array([0.5, np.nan, -1.0, 0.5, 2.0], np.float32)
+    out = po.uniform_noise(v)
+    assert np.array_equal(out, np.array([2, 0, 1, 3, 4], np.float32) / np.float32(4))

@@ -494,6 +494,36 @@ int ve_get_rivers(ve_ctx* ctx, double continent_scale_hack, const uint32_t* newh
     return VE_OK;
 }
 
+int ve_uniform_noise(ve_ctx* ctx, const float* values, float* cdf) {
+    if (!ctx || !values || !cdf) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    float* dv = (float*)ctx->elev; float* dout = (float*)ctx->deltah;
+    VE_CUDA(cudaMemcpyAsync(dv, values, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_uniform_noise(ctx, dv, dout, nullptr));
+    VE_CUDA(cudaMemcpyAsync(cdf, dout, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
+int ve_horizon_map(ve_ctx* ctx, float minh, float maxh, const float* h, float* west_angle, float* west_height,
+                   float* east_angle, float* east_height) {
+    if (!ctx || !h || !west_angle || !west_height || !east_angle || !east_height) return VE_ERR_INVALID;
+    if (maxh < minh) { ctx->err = "get_horizon_map: maxh must not be below minh"; return VE_ERR_INVALID; }   // util.rs:382-385
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    float* dh_ = (float*)ctx->elev;
+    float* o = (float*)ctx->mwrec;   // 4 * n floats needed, 16 n available
+    VE_CUDA(cudaMemcpyAsync(dh_, h, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_horizon(ctx, minh, maxh, dh_, o, o + n, o + 2 * n, o + 3 * n));
+    VE_CUDA(cudaMemcpyAsync(west_angle, o, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(west_height, o + n, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(east_angle, o + 2 * n, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(east_height, o + 3 * n, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
 int ve_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux) {
     if (!ctx || !newh || !dh || !flux) return VE_ERR_INVALID;
     VE_CUDA(cudaSetDevice(ctx->device));

@@ -134,6 +134,8 @@ int ve_g_thermal_wh(ve_ctx* ctx);           // wh running max along newh (erosio
 int ve_g_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux);
 int ve_g_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* ocean, double* out);
 int ve_g_get_oceans(ve_ctx* ctx, const double* h, uint8_t* oc);
+int ve_g_uniform_noise(ve_ctx* ctx, const float* values, float* out, uint32_t* count_out);
+int ve_g_horizon(ve_ctx* ctx, float minh, float maxh, const float* h, float* a_w, float* h_w, float* a_e, float* h_e);
 int ve_g_get_rivers(ve_ctx* ctx, double scale, const uint32_t* newh, const double* water_alt, const int32_t* dh, const int32_t* ind,
                     const double* drainage, void* out_dev);
 int ve_g_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* ocean, const int32_t* dh, const int32_t* ind,

@@ -28,7 +28,8 @@ EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_
            "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
-           "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers"]
+           "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
+           "ve_horizon_map"]
 
 
 class VeError(RuntimeError):
@@ -259,6 +260,18 @@ class ErosionContext:
                                       _p(np.ascontiguousarray(dh, np.int32)), _p(np.ascontiguousarray(indirection, np.int32)),
                                       _p(np.ascontiguousarray(drainage, np.float64)), _p(out)))
         return out
+
+    def uniform_noise(self, values):
+        v = np.ascontiguousarray(values, np.float32)
+        out = np.empty(self.n, np.float32)
+        self._chk(lib().ve_uniform_noise(self.ctx, _p(v), _p(out)))
+        return out
+
+    def horizon_map(self, minh, maxh, h):
+        hh = np.ascontiguousarray(h, np.float32)
+        outs = [np.empty(self.n, np.float32) for _ in range(4)]
+        self._chk(lib().ve_horizon_map(self.ctx, ctypes.c_float(minh), ctypes.c_float(maxh), _p(hh), *[_p(o) for o in outs]))
+        return outs
 
     def get_drainage(self, newh, dh):
         flux = np.empty(self.n, np.float32)
