@@ -88,7 +88,7 @@ def run_reference(args):
     from veloren_b200 import synth
     from oracle import pyoracle as po
     fields = synth.generate(X_LG, Y_LG)
-    o = po.Oracle(fields)
+    o = po.Oracle(fields, n_threads=os.cpu_count())   # torchrun exports OMP_NUM_THREADS=1: ask for all cores explicitly
     n = o.n
     for _ in range(args.warmup):
         o.step()
@@ -195,7 +195,7 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import pyoracle as po
-        o = po.Oracle(fields)
+        o = po.Oracle(fields, n_threads=os.cpu_count())
         o.step()
         t0 = time.perf_counter()
         cs = 3
