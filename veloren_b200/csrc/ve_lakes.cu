@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256) k_adj_build(uint32_t cap, int fill, PassT
                                                    uint32_t* __restrict__ deg, uint64_t* __restrict__ adj_ft,
                                                    uint32_t* __restrict__ adj_tgt, uint64_t* __restrict__ adj_k0,
                                                    uint64_t* __restrict__ cand_k0, uint64_t* __restrict__ cand_k1,
-                                                   uint32_t* __restrict__ cand_lr, uint32_t* __restrict__ counter) {
+                                                   uint4* __restrict__ cand_pl, uint32_t* __restrict__ counter) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= cap || t.key[s] == 0) return;
     uint64_t pk = t.key[s] - 1ull;
@@ -178,7 +178,8 @@ __global__ void __launch_bounds__(256) k_adj_build(uint32_t cap, int fill, PassT
         uint32_t i = atomicAdd(counter, 1u);
         cand_k0[i] = t.hb[s];
         cand_k1[i] = an ? (((uint64_t)ca << 32) | cb) : (((uint64_t)cb << 32) | ca);
-        cand_lr[i] = an ? lrank[A] : lrank[B];
+        uint32_t lr = an ? lrank[A] : lrank[B];
+        cand_pl[i] = make_uint4(lr, off[lr], off[lr + 1], an ? A : B);
     }
 }
 __global__ void __launch_bounds__(256) k_lake_roots(uint32_t n, const int32_t* __restrict__ dh0, const uint32_t* __restrict__ lrank,
@@ -187,8 +188,8 @@ __global__ void __launch_bounds__(256) k_lake_roots(uint32_t n, const int32_t* _
     if (i < n && dh0[i] == -1) lake_root[lrank[i]] = i;
 }
 __global__ void __launch_bounds__(256) k_gather3(uint32_t n, const uint32_t* __restrict__ idx, const uint64_t* __restrict__ a0,
-                                                 const uint64_t* __restrict__ a1, const uint32_t* __restrict__ a2,
-                                                 uint64_t* __restrict__ o0, uint64_t* __restrict__ o1, uint32_t* __restrict__ o2) {
+                                                 const uint64_t* __restrict__ a1, const uint4* __restrict__ a2,
+                                                 uint64_t* __restrict__ o0, uint64_t* __restrict__ o1, uint4* __restrict__ o2) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint32_t j = idx[i];
@@ -207,31 +208,37 @@ __global__ void __launch_bounds__(256) k_iota32(uint32_t n, uint32_t* p) {
 // ---- (iv) Prim growth, one warp ------------------------------------------------------------------
 // 32-ary min-heap on (k0, k1) with payload lr (rank of the lake the candidate would connect).
 // The first HEAP_SMEM entries (levels 0..2) live in shared memory, the rest in global memory.
-#define HEAP_SMEM_MAX 10240u   /* entries of 20 B: 200 KB of the 227 KB an SM offers */
+#define HEAP_SMEM_MAX 6400u    /* entries of 32 B: 200 KB of the 227 KB an SM offers */
 __device__ __forceinline__ bool key_less(uint64_t a0, uint64_t a1, uint64_t b0, uint64_t b1) {
     return a0 < b0 || (a0 == b0 && a1 < b1);
 }
+// payload of a heap entry: {rank of the lake it would connect, its adjacency range [b, e), its root cell},
+// fetched when the candidate is created so that a pop needs no further dependent loads
 struct Heap {
-    uint64_t* s0; uint64_t* s1; uint32_t* s2; uint64_t* g0; uint64_t* g1; uint32_t* g2; uint32_t ns;
-    __device__ __forceinline__ void get(uint32_t i, uint64_t& k0, uint64_t& k1, uint32_t& lr) const {
-        if (i < ns) { k0 = s0[i]; k1 = s1[i]; lr = s2[i]; } else { k0 = g0[i]; k1 = g1[i]; lr = g2[i]; }
+    uint64_t* s0; uint64_t* s1; uint4* s2; uint64_t* g0; uint64_t* g1; uint4* g2; uint32_t ns;
+    __device__ __forceinline__ void get(uint32_t i, uint64_t& k0, uint64_t& k1, uint4& pl) const {
+        if (i < ns) { k0 = s0[i]; k1 = s1[i]; pl = s2[i]; } else { k0 = g0[i]; k1 = g1[i]; pl = g2[i]; }
     }
-    __device__ __forceinline__ void set(uint32_t i, uint64_t k0, uint64_t k1, uint32_t lr) const {
-        if (i < ns) { s0[i] = k0; s1[i] = k1; s2[i] = lr; } else { g0[i] = k0; g1[i] = k1; g2[i] = lr; }
+    __device__ __forceinline__ void getk(uint32_t i, uint64_t& k0, uint64_t& k1) const {
+        if (i < ns) { k0 = s0[i]; k1 = s1[i]; } else { k0 = g0[i]; k1 = g1[i]; }
     }
+    __device__ __forceinline__ void set(uint32_t i, uint64_t k0, uint64_t k1, uint4 pl) const {
+        if (i < ns) { s0[i] = k0; s1[i] = k1; s2[i] = pl; } else { g0[i] = k0; g1[i] = k1; g2[i] = pl; }
+    }
+    __device__ __forceinline__ void move(uint32_t dst, uint32_t src) const { uint64_t a, b; uint4 c; get(src, a, b, c); set(dst, a, b, c); }
 };
 __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict__ lake_root, const uint32_t* __restrict__ off,
                                                      const uint64_t* __restrict__ adj_ft, const uint32_t* __restrict__ adj_tgt,
-                                                     const uint64_t* __restrict__ adj_k0, uint64_t* hk0, uint64_t* hk1, uint32_t* hk2,
+                                                     const uint64_t* __restrict__ adj_k0, uint64_t* hk0, uint64_t* hk1, uint4* hk2,
                                                      uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
                                                      uint64_t* best0, uint64_t* best1,
                                                      uint32_t* __restrict__ flows, uint32_t* __restrict__ n_flows_out,
                                                      uint32_t heap_smem, uint32_t conn_words) {
     extern __shared__ __align__(16) unsigned char heap_raw[];
-    uint64_t* s0 = (uint64_t*)heap_raw;
+    uint4* s2 = (uint4*)heap_raw;
+    uint64_t* s0 = (uint64_t*)(s2 + heap_smem);
     uint64_t* s1 = s0 + heap_smem;
-    uint32_t* s2 = (uint32_t*)(s1 + heap_smem);
-    uint32_t* cbits = s2 + heap_smem;               // "connected" bitmap (conn_words > 0), else global bytes
+    uint32_t* cbits = (uint32_t*)(s1 + heap_smem);  // "connected" bitmap (conn_words > 0), else global bytes
     const unsigned lane = threadIdx.x;
     for (uint32_t i = lane; i < conn_words; i += 32) cbits[i] = 0u;
     Heap hp{s0, s1, s2, hk0, hk1, hk2, heap_smem};
@@ -245,36 +252,45 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
     // then pushed needlessly and popped as stale, which is harmless)
     while (hn > 0) {
         n_pops++;
-        uint64_t m0, m1; uint32_t mlr;
-        hp.get(0, m0, m1, mlr);
+        uint64_t m0, m1; uint4 mp;
+        hp.get(0, m0, m1, mp);
         hn--;
         if (hn > 0) {
-            uint64_t l0, l1; uint32_t llr;
-            hp.get(hn, l0, l1, llr);
+            uint64_t l0, l1;
+            hp.getk(hn, l0, l1);
             __syncwarp();
             uint32_t i = 0;
             for (;;) { // sift down: the 32 children of i are scanned by the lanes
                 uint32_t c = 32u * i + 1u + lane;
-                uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t clr = 0, ci = c;
-                if (c < hn) hp.get(c, c0, c1, clr);
-                for (int o = 16; o > 0; o >>= 1) {
-                    uint64_t o0 = __shfl_xor_sync(0xffffffffu, c0, o), o1 = __shfl_xor_sync(0xffffffffu, c1, o);
-                    uint32_t ol = __shfl_xor_sync(0xffffffffu, clr, o), oi = __shfl_xor_sync(0xffffffffu, ci, o);
-                    if (key_less(o0, o1, c0, c1) || (o0 == c0 && o1 == c1 && oi < ci)) { c0 = o0; c1 = o1; clr = ol; ci = oi; }
+                uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t ci = c;
+                if (c < hn) hp.getk(c, c0, c1);
+                {
+                    // lexicographic min over the lanes with four 32-bit warp reductions (redux.sync) instead of
+                    // a shuffle tree on 128-bit keys: in a one-warp kernel every instruction is exposed latency
+                    const unsigned full = 0xffffffffu;
+                    uint32_t w0 = (uint32_t)(c0 >> 32), w1 = (uint32_t)c0, w2 = (uint32_t)(c1 >> 32), w3 = (uint32_t)c1;
+                    uint32_t m0r = __reduce_min_sync(full, w0); bool in = (c < hn) && (w0 == m0r);
+                    uint32_t m1r = __reduce_min_sync(full, in ? w1 : 0xffffffffu); in = in && (w1 == m1r);
+                    uint32_t m2r = __reduce_min_sync(full, in ? w2 : 0xffffffffu); in = in && (w2 == m2r);
+                    uint32_t m3r = __reduce_min_sync(full, in ? w3 : 0xffffffffu); in = in && (w3 == m3r);
+                    unsigned bal = __ballot_sync(full, in);
+                    int win = bal ? (__ffs(bal) - 1) : 0;
+                    c0 = ((uint64_t)m0r << 32) | m1r; c1 = ((uint64_t)m2r << 32) | m3r;
+                    ci = 32u * i + 1u + (uint32_t)win;
                 }
                 if (32u * i + 1u >= hn || !key_less(c0, c1, l0, l1)) break;
-                if (lane == 0) hp.set(i, c0, c1, clr);
+                if (lane == 0) hp.move(i, ci);
+                __syncwarp();
                 i = ci;
             }
-            if (lane == 0) hp.set(i, l0, l1, llr);
+            if (lane == 0 && i != hn) hp.move(i, hn);
             __syncwarp();
         }
         (void)m0;
-        // independent loads first, then the test (one round trip instead of two)
+        const uint32_t mlr = mp.x;
         bool already = conn_words ? ((cbits[mlr >> 5] >> (mlr & 31u)) & 1u) : (connected[mlr] != 0);
-        uint32_t lake = lake_root[mlr];
-        uint32_t b = off[mlr], e = off[mlr + 1];
         if (already) continue;                                        // 2085
+        const uint32_t b = mp.y, e = mp.z, lake = mp.w;
         uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
         __syncwarp();
         if (lane == 0) {
@@ -288,122 +304,37 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
         // push the reversed other passes of this lake (2107-2136); lanes evaluate edges in parallel
         for (uint32_t a0 = b; a0 < e; a0 += 32) {
             uint32_t a = a0 + lane;
-            uint64_t ft = 0, k0 = 0; bool ok = false;
+            uint64_t ft = 0, k0 = 0; bool ok = false; uint4 pl = make_uint4(0, 0, 0, 0);
             if (a < e) {
                 ft = adj_ft[a]; k0 = adj_k0[a];
                 uint32_t tg = adj_tgt[a];
                 ok = (ft != m1) && (tg != 0xffffffffu) && !(conn_words ? ((cbits[tg >> 5] >> (tg & 31u)) & 1u) : (uint32_t)connected[tg]);
-                // payload of the pushed candidate: the lake on the other side
                 if (ok) {
-                    ft = (ft << 32) | (ft >> 32); mlr = tg;           // reversed edge (to, from)
-                    ok = key_less(k0, ft, best0[tg], best1[tg]);      // only if it beats that lake's best so far
+                    ft = (ft << 32) | (ft >> 32);                     // reversed edge (to, from)
+                    uint64_t b0 = best0[tg], b1 = best1[tg];
+                    pl = make_uint4(tg, off[tg], off[tg + 1], lake_root[tg]);   // same round trip as best[]
+                    ok = key_less(k0, ft, b0, b1);                    // only if it beats that lake's best so far
                 }
             }
             unsigned bal = __ballot_sync(0xffffffffu, ok);
             while (bal) {
                 int src = __ffs(bal) - 1; bal &= bal - 1;
                 uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
-                uint32_t plr = __shfl_sync(0xffffffffu, mlr, src);
+                uint4 pp;
+                pp.x = __shfl_sync(0xffffffffu, pl.x, src); pp.y = __shfl_sync(0xffffffffu, pl.y, src);
+                pp.z = __shfl_sync(0xffffffffu, pl.z, src); pp.w = __shfl_sync(0xffffffffu, pl.w, src);
                 if (lane == 0) { // sift up
-                    best0[plr] = p0; best1[plr] = p1;   // ok => this candidate beats the lake's best so far
+                    best0[pp.x] = p0; best1[pp.x] = p1;   // ok => this candidate beats the lake's best so far
                     uint32_t i = hn;
                     while (i > 0) {
                         uint32_t pi = (i - 1u) / 32u;
-                        uint64_t q0, q1; uint32_t qlr;
-                        hp.get(pi, q0, q1, qlr);
+                        uint64_t q0, q1;
+                        hp.getk(pi, q0, q1);
                         if (!key_less(p0, p1, q0, q1)) break;
-                        hp.set(i, q0, q1, qlr);
+                        hp.move(i, pi);
                         i = pi;
                     }
-                    hp.set(i, p0, p1, plr);
-                }
-                hn++; n_push++;
-                __syncwarp();
-            }
-        }
-    }
-    if (lane == 0) { *n_flows_out = n_flows; n_flows_out[1] = n_pops; n_flows_out[2] = n_push; }
-}
-
-// Variant for lake graphs whose whole heap fits in shared memory (the common case after the first
-// few erosion steps): a 4-ary heap driven by lane 0 alone is several times cheaper per operation than
-// the warp-wide 32-ary heap above; the lanes still evaluate a lake's adjacency entries in parallel.
-__global__ void __launch_bounds__(32) k_lake_connect_small(const uint32_t* __restrict__ lake_root, const uint32_t* __restrict__ off,
-                                                           const uint64_t* __restrict__ adj_ft, const uint32_t* __restrict__ adj_tgt,
-                                                           const uint64_t* __restrict__ adj_k0, const uint64_t* __restrict__ hk0,
-                                                           const uint64_t* __restrict__ hk1, const uint32_t* __restrict__ hk2,
-                                                           uint32_t hn0, int32_t* dh, int32_t* indirection, uint8_t* connected,
-                                                           uint64_t* best0, uint64_t* best1, uint32_t* __restrict__ flows,
-                                                           uint32_t* __restrict__ n_flows_out, uint32_t cap) {
-    extern __shared__ __align__(16) unsigned char heap_raw[];
-    uint64_t* s0 = (uint64_t*)heap_raw;
-    uint64_t* s1 = s0 + cap;
-    uint32_t* s2 = (uint32_t*)(s1 + cap);
-    const unsigned lane = threadIdx.x;
-    for (uint32_t i = lane; i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
-    __syncwarp();
-    uint32_t hn = hn0, n_flows = 0, n_pops = 0, n_push = 0;
-    while (hn > 0) {
-        n_pops++;
-        uint64_t m1 = 0; uint32_t mlr = 0;
-        if (lane == 0) {
-            m1 = s1[0]; mlr = s2[0];
-            uint32_t nh = hn - 1;
-            if (nh > 0) {
-                uint64_t l0 = s0[nh], l1 = s1[nh]; uint32_t llr = s2[nh];
-                uint32_t i = 0;
-                for (;;) {
-                    uint32_t c = 4u * i + 1u;
-                    if (c >= nh) break;
-                    uint32_t bi = c; uint64_t b0 = s0[c], b1 = s1[c];
-                    uint32_t ce = c + 4u < nh ? c + 4u : nh;
-                    for (uint32_t j = c + 1u; j < ce; ++j) { uint64_t j0 = s0[j], j1 = s1[j]; if (key_less(j0, j1, b0, b1)) { b0 = j0; b1 = j1; bi = j; } }
-                    if (!key_less(b0, b1, l0, l1)) break;
-                    s0[i] = b0; s1[i] = b1; s2[i] = s2[bi];
-                    i = bi;
-                }
-                s0[i] = l0; s1[i] = l1; s2[i] = llr;
-            }
-        }
-        hn--;
-        m1 = __shfl_sync(0xffffffffu, m1, 0); mlr = __shfl_sync(0xffffffffu, mlr, 0);
-        uint8_t already = connected[mlr];
-        uint32_t lake = lake_root[mlr];
-        uint32_t b = off[mlr], e = off[mlr + 1];
-        if (already) continue;                                        // 2085
-        uint32_t from = (uint32_t)(m1 >> 32), to = (uint32_t)m1;
-        if (lane == 0) {
-            connected[mlr] = 1;
-            dh[lake] = (int32_t)to;                                   // 2098
-            indirection[lake] = -(int32_t)from;                       // 2103
-            flows[n_flows] = lake;                                    // 2105
-        }
-        n_flows++;
-        __syncwarp();
-        for (uint32_t a0 = b; a0 < e; a0 += 32) {
-            uint32_t a = a0 + lane;
-            uint64_t ft = 0, k0 = 0; uint32_t tg = 0; bool ok = false;
-            if (a < e) {
-                ft = adj_ft[a]; k0 = adj_k0[a]; tg = adj_tgt[a];
-                ok = (ft != m1) && (tg != 0xffffffffu) && !connected[tg];
-                if (ok) { ft = (ft << 32) | (ft >> 32); ok = key_less(k0, ft, best0[tg], best1[tg]); }
-            }
-            unsigned bal = __ballot_sync(0xffffffffu, ok);
-            while (bal) {
-                int src = __ffs(bal) - 1; bal &= bal - 1;
-                uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
-                uint32_t plr = __shfl_sync(0xffffffffu, tg, src);
-                if (lane == 0) {
-                    best0[plr] = p0; best1[plr] = p1;   // ok => this candidate beats the lake's best so far
-                    uint32_t i = hn;
-                    while (i > 0) {
-                        uint32_t pi = (i - 1u) >> 2;
-                        uint64_t q0 = s0[pi], q1 = s1[pi];
-                        if (!key_less(p0, p1, q0, q1)) break;
-                        s0[i] = q0; s1[i] = q1; s2[i] = s2[pi];
-                        i = pi;
-                    }
-                    s0[i] = p0; s1[i] = p1; s2[i] = plr;
+                    hp.set(i, p0, p1, pp);
                 }
                 hn++; n_push++;
                 __syncwarp();
@@ -676,38 +607,40 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
         pc.mark("pass table");
         // adjacency (CSR over non-boundary lakes)
-        uint32_t *deg, *off, *lake_root, *adj_tgt, *cand_lr, *cand_lr_s, *cidx, *cidx2; uint64_t *adj_ft, *adj_k0, *ck0, *ck1, *ck0s, *ck1s;
+        uint32_t *deg, *off, *lake_root, *adj_tgt, *cidx, *cidx2; uint64_t *adj_ft, *adj_k0, *ck0, *ck1, *ck0s, *ck1s; uint4 *cand_pl, *cand_pl_s;
         size_t lk = (size_t)n_lakes + 1;
         uint8_t* ab;
         size_t adj_cap = 2 * (size_t)n_cross + 2;
         size_t lk16 = ((lk * 4 + 15) / 16) * 16, ac8 = adj_cap * 8, ac4 = ((adj_cap * 4 + 15) / 16) * 16;
         size_t lk8 = ((lk * 8 + 15) / 16) * 16;
-        VE_TRY(ve_scratch(ctx, 7, lk16 * 3 + ac8 * 6 + ac4 * 5 + lk8 * 2 + 256, (void**)&ab));
+        size_t ac16 = adj_cap * 16;
+        VE_TRY(ve_scratch(ctx, 7, lk16 * 3 + ac16 * 2 + ac8 * 6 + ac4 * 3 + lk8 * 2 + 256, (void**)&ab));
         deg = (uint32_t*)ab; off = (uint32_t*)(ab + lk16); lake_root = (uint32_t*)(ab + 2 * lk16);
         uint8_t* q = ab + 3 * lk16;
+        cand_pl = (uint4*)q; q += ac16; cand_pl_s = (uint4*)q; q += ac16;
         adj_ft = (uint64_t*)q; q += ac8; adj_k0 = (uint64_t*)q; q += ac8; ck0 = (uint64_t*)q; q += ac8; ck1 = (uint64_t*)q; q += ac8;
         ck0s = (uint64_t*)q; q += ac8; ck1s = (uint64_t*)q; q += ac8;
-        adj_tgt = (uint32_t*)q; q += ac4; cand_lr = (uint32_t*)q; q += ac4; cand_lr_s = (uint32_t*)q; q += ac4;
+        adj_tgt = (uint32_t*)q; q += ac4;
         cidx = (uint32_t*)q; q += ac4; cidx2 = (uint32_t*)q; q += ac4;
         uint64_t* best0 = (uint64_t*)q; q += lk8; uint64_t* best1 = (uint64_t*)q; q += lk8;
         VE_CUDA(cudaMemsetAsync(best0, 0xff, lk8 * 2, st));
         VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
         k_lake_roots<<<nb, 256, 0, st>>>(n, dh0, lrank, lake_root);
         VE_LAUNCH_CHECK();
-        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 0, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_lr, small + 3);
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 0, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_pl, small + 3);
         VE_LAUNCH_CHECK();
         cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, deg, off, (int)lk, st);
         VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
         VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, deg, off, (int)lk, st));
         ctx->launches += 2;
         VE_CUDA(cudaMemsetAsync(deg, 0, lk * 4, st));
-        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_lr, small + 3);
+        k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_pl, small + 3);
         VE_LAUNCH_CHECK();
         uint32_t n_cand = 0;
         VE_CUDA(cudaMemcpyAsync(&n_cand, small + 3, 4, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
         // initial heap = candidates sorted by (k0, k1) (a sorted array is a valid heap): LSD, k1 first
-        uint64_t *h0 = ck0, *h1 = ck1; uint32_t* h2 = cand_lr;
+        uint64_t *h0 = ck0, *h1 = ck1; uint4* h2 = cand_pl;
         if (n_cand > 1) {
             unsigned cb = ve_blocks(n_cand, 256);
             uint64_t* keytmp = ck0s;       // sorted-key output we do not need
@@ -721,9 +654,9 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
             VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck1s, keytmp, cidx2, cidx, (int)n_cand, 0, 64, st));
             // cidx = permutation sorted by (k0, k1); gather the three columns into the heap arrays
             uint64_t* g0 = ck0s; uint64_t* g1 = ck1s;
-            k_gather3<<<cb, 256, 0, st>>>(n_cand, cidx, ck0, ck1, cand_lr, g0, g1, cand_lr_s);
+            k_gather3<<<cb, 256, 0, st>>>(n_cand, cidx, ck0, ck1, cand_pl, g0, g1, cand_pl_s);
             VE_LAUNCH_CHECK();
-            h0 = g0; h1 = g1; h2 = cand_lr_s;
+            h0 = g0; h1 = g1; h2 = cand_pl_s;
             ctx->launches += 8;
         }
         pc.mark("adjacency");
@@ -731,30 +664,17 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
         {
-            uint32_t n_adj = 0;
-            VE_CUDA(cudaMemcpyAsync(&n_adj, off + n_lakes, 4, cudaMemcpyDeviceToHost, st));
-            VE_CUDA(cudaStreamSynchronize(st));
-            size_t live_max = (size_t)n_cand + (size_t)n_adj + 8;   // every entry is pushed at most once
             static bool attr_set = false;
             if (!attr_set) {
-                VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20)));
-                VE_CUDA(cudaFuncSetAttribute(k_lake_connect_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 20)));
+                VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 32)));
                 attr_set = true;
             }
-            if (getenv("VE_FORCE_SMALL") && n_lakes < 3300) live_max = HEAP_SMEM_MAX;
-            if (live_max <= HEAP_SMEM_MAX) {
-                uint32_t cap_s = (uint32_t)live_max;
-                k_lake_connect_small<<<1, 32, (size_t)cap_s * 20, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh, indirection,
-                                                                       connected, best0, best1, flows, small + 12, cap_s);
-            } else {
-                // heap entries kept in shared memory: the top of the heap, up to 200 KB
-                // shared memory: connected bitmap first (if it fits), the top of the heap in what is left
-                uint32_t conn_words = (uint32_t)((lk + 31) / 32);
-                if ((size_t)conn_words * 4 > 96 * 1024) conn_words = 0;
-                uint32_t heap_smem = (uint32_t)((HEAP_SMEM_MAX * 20 - (size_t)conn_words * 4) / 20);
-                k_lake_connect<<<1, 32, (size_t)heap_smem * 20 + (size_t)conn_words * 4, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh,
-                                                                      indirection, connected, best0, best1, flows, small + 12, heap_smem, conn_words);
-            }
+            // shared memory: connected bitmap first (if it fits), the top of the heap in what is left
+            uint32_t conn_words = (uint32_t)((lk + 31) / 32);
+            if ((size_t)conn_words * 4 > 96 * 1024) conn_words = 0;
+            uint32_t heap_smem = (uint32_t)((HEAP_SMEM_MAX * 32 - (size_t)conn_words * 4) / 32);
+            k_lake_connect<<<1, 32, (size_t)heap_smem * 32 + (size_t)conn_words * 4, st>>>(lake_root, off, adj_ft, adj_tgt, adj_k0, h0, h1, h2, n_cand, dh,
+                                                                  indirection, connected, best0, best1, flows, small + 12, heap_smem, conn_words);
         }
         VE_LAUNCH_CHECK();
         uint32_t cstat[3] = {0, 0, 0};
