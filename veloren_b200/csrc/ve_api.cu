@@ -129,8 +129,6 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     memset(ctx->timers, 0, sizeof(ctx->timers));
     memset(&ctx->nz, 0, sizeof(ctx->nz));
     ve_default_params(&ctx->P);
-    ctx->hop_down_ns = getenv("VE_HOP_DOWN_NS") ? (uint32_t)atoi(getenv("VE_HOP_DOWN_NS")) : 600u;
-    ctx->hop_up_ns = getenv("VE_HOP_UP_NS") ? (uint32_t)atoi(getenv("VE_HOP_UP_NS")) : 1200u;
     // nodes per warp in the dataflow sweeps: 1 up to 4096^2 (lanes of one warp in different phases
     // are serialised by the SIMT hardware, which stretches the critical path; measured faster at
     // 1024^2..4096^2), 8 beyond, where node throughput of 1-node warps would bound the sweep

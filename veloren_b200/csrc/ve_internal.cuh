@@ -65,7 +65,6 @@ struct ve_ctx {
     int32_t *sill_cur, *sill_prev;
     uint32_t *order_td;       // topological order, sources first (wh desc, stack position asc)
     uint32_t *level;          // longest path to a sink, per node
-    uint32_t hop_down_ns, hop_up_ns; // per-level sleep estimates of the GS sweeps
     uint32_t lanes_down, lanes_up, lanes_other;   // active lanes per warp in the sweeps
     uint32_t *order_bu;       // nodes sorted by level (longest path to a sink): sinks first
     uint32_t *don_order;      // packed donor slots sorted by stack position
