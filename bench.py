@@ -29,7 +29,7 @@ X_LG = Y_LG = 10
 # algorithmic bytes per cell of the dominant kernel (G4, the implicit up-sweep)
 G4_BYTES_PER_CELL = 145
 FIXED_BYTES_PER_CELL, GS_BYTES_PER_CELL = 684, 374
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_dataflow<OpGsUp> launch (ncu --set full, round 1)
+# dram__bytes_read.sum + dram__bytes_write.sum of one up-sweep launch (ncu --set full, round 1)
 NCU_TRAFFIC_BYTES = 66126848 + 15436032
 
 
@@ -165,7 +165,7 @@ def run_ours(args):
     peak, how = peaks()
     per_launch = up_s / max(n_gs_tot, 1)
     achieved = G4_BYTES_PER_CELL * n / per_launch / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_dataflow<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
+    roofline = {"bound": "hbm", "kernel": "k_sweep_warp<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
                 "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r01_ncu_full_OpGsUp.txt (dram read 66.13 MB + write 15.44 MB per launch)", "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
                 "n_gs_per_step": gs_counts}

@@ -71,6 +71,23 @@ def test_c5_plateau_256_lake_heavy():
         _assert_step_equal(o, c, "C5 step %d" % it)
 
 
+def test_thread_per_node_sweeps_match_too(monkeypatch):
+    """Maps beyond 4096^2 run the sweeps with several nodes per warp (one thread per node) instead of
+    one warp per node; force that path on a small map (the lane counts are read at ve_create)."""
+    for k in ("VE_LANES_UP", "VE_LANES_DOWN", "VE_LANES_OTHER"):
+        monkeypatch.setenv(k, "8")
+    f = synth.generate(7, 7)
+    o, c = po.Oracle(f), _ctx(f)
+    for it in range(3):
+        o.step(); c.step()
+        _assert_step_equal(o, c, "lanes=8 step %d" % it)
+    g = synth.generate(7, 7, kind=1)
+    o, c = po.Oracle(g), _ctx(g)
+    for it in range(2):
+        o.step(); c.step()
+        _assert_step_equal(o, c, "lanes=8 plateau step %d" % it)
+
+
 def test_non_square_and_small_maps():
     for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
         f = synth.generate(x_lg, y_lg)

@@ -245,6 +245,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
     for (uint32_t i = lane; i < heap_smem && i < hn0; i += 32) { s0[i] = hk0[i]; s1[i] = hk1[i]; s2[i] = hk2[i]; }
     __syncwarp();
     uint32_t hn = hn0, n_flows = 0, n_pops = 0, n_push = 0;
+    long long t_sift = 0, t_scan = 0, t_push = 0, tc;
     // best[l] = smallest key pushed so far for lake l.  A candidate that is not smaller can never be
     // the one that connects l (the smaller one is popped first and is never stale before l is
     // connected), so it is not pushed at all: same result as the reference's heap, fewer heap ops.
@@ -252,6 +253,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
     // then pushed needlessly and popped as stale, which is harmless)
     while (hn > 0) {
         n_pops++;
+        tc = clock64();
         uint64_t m0, m1; uint4 mp;
         hp.get(0, m0, m1, mp);
         hn--;
@@ -287,6 +289,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
             __syncwarp();
         }
         (void)m0;
+        t_sift += clock64() - tc;
         const uint32_t mlr = mp.x;
         bool already = conn_words ? ((cbits[mlr >> 5] >> (mlr & 31u)) & 1u) : (connected[mlr] != 0);
         if (already) continue;                                        // 2085
@@ -303,6 +306,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
         __syncwarp();
         // push the reversed other passes of this lake (2107-2136); lanes evaluate edges in parallel
         for (uint32_t a0 = b; a0 < e; a0 += 32) {
+            tc = clock64();
             uint32_t a = a0 + lane;
             uint64_t ft = 0, k0 = 0; bool ok = false; uint4 pl = make_uint4(0, 0, 0, 0);
             if (a < e) {
@@ -317,6 +321,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 }
             }
             unsigned bal = __ballot_sync(0xffffffffu, ok);
+            t_scan += clock64() - tc; tc = clock64();
             while (bal) {
                 int src = __ffs(bal) - 1; bal &= bal - 1;
                 uint64_t p0 = __shfl_sync(0xffffffffu, k0, src), p1 = __shfl_sync(0xffffffffu, ft, src);
@@ -339,9 +344,11 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 hn++; n_push++;
                 __syncwarp();
             }
+            t_push += clock64() - tc;
         }
     }
-    if (lane == 0) { *n_flows_out = n_flows; n_flows_out[1] = n_pops; n_flows_out[2] = n_push; }
+    if (lane == 0) { *n_flows_out = n_flows; n_flows_out[1] = n_pops; n_flows_out[2] = n_push;
+                     n_flows_out[3] = (uint32_t)(t_sift >> 10); n_flows_out[4] = (uint32_t)(t_scan >> 10); n_flows_out[5] = (uint32_t)(t_push >> 10); }
 }
 
 // ---- (v) per-lake flood -----------------------------------------------------------------------------
@@ -677,11 +684,11 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
                                                                   indirection, connected, best0, best1, flows, small + 12, heap_smem, conn_words);
         }
         VE_LAUNCH_CHECK();
-        uint32_t cstat[3] = {0, 0, 0};
-        VE_CUDA(cudaMemcpyAsync(cstat, small + 12, 12, cudaMemcpyDeviceToHost, st));
+        uint32_t cstat[6] = {0, 0, 0, 0, 0, 0};
+        VE_CUDA(cudaMemcpyAsync(cstat, small + 12, 24, cudaMemcpyDeviceToHost, st));
         VE_CUDA(cudaStreamSynchronize(st));
         n_flows = cstat[0];
-        if (pc.on) fprintf(stderr, "[lakes] lakes %u cand %u pops %u pushes %u\n", n_lakes, n_cand, cstat[1], cstat[2]);
+        if (pc.on) fprintf(stderr, "[lakes] lakes %u cand %u pops %u pushes %u; kcycles sift %u scan %u push %u\n", n_lakes, n_cand, cstat[1], cstat[2], cstat[3], cstat[4], cstat[5]);
         if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
         pc.mark("connect");
         // (v) flood: per-lake stacks carved out of one array by an exclusive scan of tree sizes
