@@ -344,13 +344,20 @@ int ve_k_thermal_kd(ve_ctx* ctx) {
 
 // ---------------------------------------------------------------------------------------------
 // E13: ADI hillslope diffusion (diffusion.rs:41-394) with the Thomas solver (408-472).
-// One thread per line keeps the reference's operation order, hence bit-exact results.
+// One WARP per line.  The Thomas recurrence itself is serial and keeps the reference's operation
+// order (bit-exact): ~130 cycles per element (one f64 division on the chain).  What made a
+// thread-per-line version 10x slower than that chain was its nine loads per element with nothing to
+// overlap them; here the lanes build the coefficients of 32 consecutive elements at once
+// (coalesced along rows), the recurrence then runs out of registers in every lane alike (values by
+// shuffle, so the warp stays converged), and lane j keeps element j's results for a coalesced store.
 // dir 0: x-sweep over rows 1..ny-2 (reads zp = original h for the explicit y terms, writes z).
 // dir 1: y-sweep over columns 1..nx-2 (reads z = x-sweep result, writes zp).
-__global__ void __launch_bounds__(64) k_adi_sweep(int nx, int ny, int dir, double dt, const double* __restrict__ kd,
-                                                  const double* __restrict__ src, double* __restrict__ dst,
-                                                  double* __restrict__ gam, int* __restrict__ fail) {
-    int line = blockIdx.x * blockDim.x + threadIdx.x + 1;
+__global__ void __launch_bounds__(128) k_adi_sweep(int nx, int ny, int dir, double dt, const double* __restrict__ kd,
+                                                   const double* __restrict__ src, double* __restrict__ dst,
+                                                   double* __restrict__ gam, int* __restrict__ fail) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int line = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1;
     int nlines = dir == 0 ? ny : nx;
     if (line >= nlines - 1) return;
     const int n = dir == 0 ? nx : ny;
@@ -360,45 +367,65 @@ __global__ void __launch_bounds__(64) k_adi_sweep(int nx, int ny, int dir, doubl
     const double dx = 32.0, dy = 32.0;            // xl/nx, yl/ny with xl = nx*32 (erosion.rs:1720-1721)
     const double ca = dir == 0 ? (dx * dx) : (dy * dy); // along-line spacing^2
     const double cc = dir == 0 ? (dy * dy) : (dx * dx); // cross-line spacing^2
-    // j = 0 : Dirichlet
-    double bet = 1.0;
-    double uprev = src[base] / bet;
-    dst[base] = uprev;
-    double prev_sup = 0.0;
+    // forward elimination.  Element 0 (Dirichlet) goes through the same recurrence as the last one:
+    // with diag 1, inf 0 and the initial bet = 1, prev_sup = 0 it yields u = src / 1 exactly.
+    double bet = 1.0, uprev = 0.0, prev_sup = 0.0;
     bool bad = false;
-    for (int i = 1; i < n; ++i) {
-        long long ij = base + (long long)i * sa;
-        double inf_i, diag_i, sup_i, f_i;
-        if (i < n - 1) {
-            double kc = kd[ij];
-            double fap = (kd[ij + sa] + kc) / 2.0 * (dt / 2.0) / ca;
-            double fam = (kd[ij - sa] + kc) / 2.0 * (dt / 2.0) / ca;
-            double fcp = (kd[ij + sc] + kc) / 2.0 * (dt / 2.0) / cc;
-            double fcm = (kd[ij - sc] + kc) / 2.0 * (dt / 2.0) / cc;
-            diag_i = 1.0 + fap + fam;
-            sup_i = -fap;
-            inf_i = -fam;
-            f_i = src[ij] + fcp * src[ij + sc] - (fcp + fcm) * src[ij] + fcm * src[ij - sc];
-        } else {
-            diag_i = 1.0; inf_i = 0.0; sup_i = 0.0; f_i = src[ij];
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const long long ij = base + (long long)i * sa;
+        double inf_i = 0.0, diag_i = 1.0, sup_i = 0.0, f_i = 0.0;
+        if (i < n) {
+            if (i > 0 && i < n - 1) {
+                double kc = kd[ij];
+                double fap = (kd[ij + sa] + kc) / 2.0 * (dt / 2.0) / ca;
+                double fam = (kd[ij - sa] + kc) / 2.0 * (dt / 2.0) / ca;
+                double fcp = (kd[ij + sc] + kc) / 2.0 * (dt / 2.0) / cc;
+                double fcm = (kd[ij - sc] + kc) / 2.0 * (dt / 2.0) / cc;
+                diag_i = 1.0 + fap + fam;
+                sup_i = -fap;
+                inf_i = -fam;
+                f_i = src[ij] + fcp * src[ij + sc] - (fcp + fcm) * src[ij] + fcm * src[ij - sc];
+            } else {
+                f_i = src[ij];
+            }
         }
-        double gm = prev_sup / bet;
-        gam[ij] = gm;
-        bet = diag_i - inf_i * gm;
-        if (bet == 0.0) bad = true;
-        uprev = (f_i - inf_i * uprev) / bet;
-        dst[ij] = uprev;
-        prev_sup = sup_i;
+        const int cnt = min(32, n - i0);
+        double my_gam = 0.0, my_u = 0.0;
+#pragma unroll 8
+        for (int j = 0; j < cnt; ++j) {
+            double inf_j = __shfl_sync(FULL, inf_i, j), diag_j = __shfl_sync(FULL, diag_i, j);
+            double f_j = __shfl_sync(FULL, f_i, j), sup_j = __shfl_sync(FULL, sup_i, j);
+            double gm = prev_sup / bet;
+            bet = diag_j - inf_j * gm;
+            if (bet == 0.0) bad = true;
+            uprev = (f_j - inf_j * uprev) / bet;
+            prev_sup = sup_j;
+            if (lane == j) { my_gam = gm; my_u = uprev; }
+        }
+        if (i < n) { if (i > 0) gam[ij] = my_gam; dst[ij] = my_u; }
     }
-    double unext = uprev;
-    for (int i = n - 2; i >= 0; --i) {
-        long long ij = base + (long long)i * sa;
-        double u = dst[ij];
-        u -= gam[ij + sa] * unext;
-        dst[ij] = u;
-        unext = u;
+    __syncwarp();
+    // back substitution, chunks from the end
+    double unext = 0.0;
+    for (int i0 = ((n - 1) / 32) * 32; i0 >= 0; i0 -= 32) {
+        const int i = i0 + lane;
+        const long long ij = base + (long long)i * sa;
+        double d_i = 0.0, g_i = 0.0;
+        if (i < n) { d_i = dst[ij]; if (i < n - 1) g_i = gam[ij + sa]; }
+        const int cnt = min(32, n - i0);
+        double my_u = 0.0;
+#pragma unroll 8
+        for (int j = cnt - 1; j >= 0; --j) {
+            double d_j = __shfl_sync(FULL, d_i, j), g_j = __shfl_sync(FULL, g_i, j);
+            double u = d_j;
+            if (i0 + j < n - 1) u -= g_j * unext;
+            unext = u;
+            if (lane == j) my_u = u;
+        }
+        if (i < n - 1) dst[ij] = my_u;
     }
-    if (bad) *fail = 1;
+    if (bad && lane == 0) *fail = 1;
 }
 
 __global__ void __launch_bounds__(256) k_adi_finish(uint32_t n, const double* __restrict__ zp, double* __restrict__ h,
@@ -422,9 +449,9 @@ int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* k
     // zint = h; zintp = zint.clone()  (diffusion.rs:108-120); kdsed = -1 keeps kdint = kd_eff
     VE_CUDA(cudaMemcpyAsync(z, h, nb, cudaMemcpyDeviceToDevice, ctx->stream));
     VE_CUDA(cudaMemcpyAsync(zp, h, nb, cudaMemcpyDeviceToDevice, ctx->stream));
-    k_adi_sweep<<<ve_blocks(g.ny, 64), 64, 0, ctx->stream>>>(g.nx, g.ny, 0, dt, kd_eff, zp, z, gam, fail);
+    k_adi_sweep<<<ve_blocks((uint64_t)g.ny * 32, 128), 128, 0, ctx->stream>>>(g.nx, g.ny, 0, dt, kd_eff, zp, z, gam, fail);
     VE_LAUNCH_CHECK();
-    k_adi_sweep<<<ve_blocks(g.nx, 64), 64, 0, ctx->stream>>>(g.nx, g.ny, 1, dt, kd_eff, z, zp, gam, fail);
+    k_adi_sweep<<<ve_blocks((uint64_t)g.nx * 32, 128), 128, 0, ctx->stream>>>(g.nx, g.ny, 1, dt, kd_eff, z, zp, gam, fail);
     VE_LAUNCH_CHECK();
     k_adi_finish<<<ve_blocks(g.n, 256), 256, 0, ctx->stream>>>(g.n, zp, h, b);
     VE_LAUNCH_CHECK();
@@ -514,9 +541,9 @@ extern "C" int ve_diffusion_static(uint32_t x_lg, uint32_t y_lg, double dt, doub
     ST_CUDA(cudaMemsetAsync(fail, 0, sizeof(int), st));
     ST_CUDA(cudaMemcpyAsync(z, d_h, nb, cudaMemcpyDeviceToDevice, st));
     ST_CUDA(cudaMemcpyAsync(zp, d_h, nb, cudaMemcpyDeviceToDevice, st));
-    k_adi_sweep<<<ve_blocks(ny, 64), 64, 0, st>>>(nx, ny, 0, dt, d_kd_eff, zp, z, gam, fail);
+    k_adi_sweep<<<ve_blocks((uint64_t)ny * 32, 128), 128, 0, st>>>(nx, ny, 0, dt, d_kd_eff, zp, z, gam, fail);
     ST_CUDA(cudaGetLastError());
-    k_adi_sweep<<<ve_blocks(nx, 64), 64, 0, st>>>(nx, ny, 1, dt, d_kd_eff, z, zp, gam, fail);
+    k_adi_sweep<<<ve_blocks((uint64_t)nx * 32, 128), 128, 0, st>>>(nx, ny, 1, dt, d_kd_eff, z, zp, gam, fail);
     ST_CUDA(cudaGetLastError());
     k_adi_finish<<<ve_blocks(n, 256), 256, 0, st>>>(n, zp, d_h, d_b);
     ST_CUDA(cudaGetLastError());
