@@ -88,6 +88,17 @@ def test_thread_per_node_sweeps_match_too(monkeypatch):
         _assert_step_equal(o, c, "lanes=8 plateau step %d" % it)
 
 
+def test_newton_fallback_path_matches(monkeypatch):
+    """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with
+    the plain operators if a range test ever failed; VE_DBG=4 forces the second solve for every node."""
+    monkeypatch.setenv("VE_DBG", "4")
+    f = synth.generate(7, 7)
+    o, c = po.Oracle(f), _ctx(f)
+    for it in range(3):
+        o.step(); c.step()
+        _assert_step_equal(o, c, "forced fallback step %d" % it)
+
+
 def test_non_square_and_small_maps():
     for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
         f = synth.generate(x_lg, y_lg)
