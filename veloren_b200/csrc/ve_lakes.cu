@@ -262,6 +262,36 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
             hp.getk(hn, l0, l1);
             __syncwarp();
             uint32_t i = 0;
+            if (hn < heap_smem) {
+                // whole heap in shared memory (the usual case): no smem/global tests, and every lane performs
+                // the moves (same addresses, same values) - a one-warp kernel pays for every branch region
+                const unsigned full = 0xffffffffu;
+                for (;;) {
+                    const uint32_t cb = 32u * i + 1u;
+                    if (cb >= hn) break;
+                    const uint32_t c = cb + lane;
+                    const bool valid = c < hn;
+                    const uint32_t cc = valid ? c : 0u;
+                    uint64_t c0 = s0[cc], c1 = s1[cc];
+                    if (!valid) { c0 = ~0ull; c1 = ~0ull; }
+                    uint32_t w0 = (uint32_t)(c0 >> 32), w1 = (uint32_t)c0, w2 = (uint32_t)(c1 >> 32), w3 = (uint32_t)c1;
+                    uint32_t m0r = __reduce_min_sync(full, w0); bool in = valid && (w0 == m0r);
+                    uint32_t m1r = __reduce_min_sync(full, in ? w1 : 0xffffffffu); in = in && (w1 == m1r);
+                    uint32_t m2r = __reduce_min_sync(full, in ? w2 : 0xffffffffu); in = in && (w2 == m2r);
+                    uint32_t m3r = __reduce_min_sync(full, in ? w3 : 0xffffffffu); in = in && (w3 == m3r);
+                    unsigned bal = __ballot_sync(full, in);
+                    const uint32_t ci = cb + (uint32_t)(bal ? (__ffs(bal) - 1) : 0);
+                    c0 = ((uint64_t)m0r << 32) | m1r; c1 = ((uint64_t)m2r << 32) | m3r;
+                    if (!key_less(c0, c1, l0, l1)) break;
+                    uint4 pl = s2[ci];
+                    __syncwarp();
+                    s0[i] = c0; s1[i] = c1; s2[i] = pl;
+                    __syncwarp();
+                    i = ci;
+                }
+                if (i != hn) { uint4 pl = s2[hn]; __syncwarp(); s0[i] = l0; s1[i] = l1; s2[i] = pl; }
+                __syncwarp();
+            } else {
             for (;;) { // sift down: the 32 children of i are scanned by the lanes
                 uint32_t c = 32u * i + 1u + lane;
                 uint64_t c0 = ~0ull, c1 = ~0ull; uint32_t ci = c;
@@ -287,6 +317,7 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
             }
             if (lane == 0 && i != hn) hp.move(i, hn);
             __syncwarp();
+            }
         }
         (void)m0;
         t_sift += clock64() - tc;
