@@ -129,10 +129,10 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     memset(ctx->timers, 0, sizeof(ctx->timers));
     memset(&ctx->nz, 0, sizeof(ctx->nz));
     ve_default_params(&ctx->P);
-    // nodes per warp in the dataflow sweeps: 1 up to 4096^2 (lanes of one warp in different phases
-    // are serialised by the SIMT hardware, which stretches the critical path; measured faster at
-    // 1024^2..4096^2), 8 beyond, where node throughput of 1-node warps would bound the sweep
-    uint32_t auto_lanes = (x_lg + y_lg > 24) ? 8u : 1u;
+    // Sweeps run one warp per node at every map size (measured: 1024^2 .. 8192^2; at 8192^2 the up-sweep
+    // takes 0.53 s per step against 1.1 s with eight one-thread nodes per warp).  VE_LANES_* > 1 selects
+    // the thread-per-node kernels instead (kept for comparison and covered by a test).
+    uint32_t auto_lanes = 1u;
     ctx->lanes_down = getenv("VE_LANES_DOWN") ? (uint32_t)atoi(getenv("VE_LANES_DOWN")) : auto_lanes;
     ctx->lanes_up = getenv("VE_LANES_UP") ? (uint32_t)atoi(getenv("VE_LANES_UP")) : auto_lanes;
     ctx->lanes_other = getenv("VE_LANES_OTHER") ? (uint32_t)atoi(getenv("VE_LANES_OTHER")) : auto_lanes;
