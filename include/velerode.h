@@ -94,6 +94,14 @@ const char* ve_last_error(ve_ctx* ctx);
 
 int ve_set_params(ve_ctx* ctx, const ve_params* p);
 int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz);
+/* Alternative rock-strength source for get_max_slope (erosion.rs:550-604): the host's own
+ * `rock_strength_nz: impl NoiseFn<f64, 3>` (erosion.rs:2529), for exact parity with an arbitrary
+ * noise-rs function.  Once per erode() the library hands the callback the N sample points
+ * (xyz interleaved, the argument of `.get()` at erosion.rs:585-589) and reads N values back; the
+ * callback runs on the calling thread.  Costs one 24N-byte download and one 8N-byte upload per step.
+ * cb == NULL returns to the table set with ve_set_noise. */
+typedef void (*ve_noise_cb)(void* user, const double* xyz, double* out, size_t n);
+int ve_set_noise_cb(ve_ctx* ctx, ve_noise_cb cb, void* user);
 /* Uploads the inputs and initialises h = oldh as f64, b = oldb as f64, wh = 0
  * (erosion.rs:2549-2559, 2601); computes max_uplift and max_g (2617-2626). */
 int ve_set_inputs(ve_ctx* ctx, const ve_inputs* in);

@@ -689,6 +689,13 @@ void orc_set_noise(orc_ctx* c, const orc_noise* nz) {
     c->nz.persistence = nz->persistence; c->nz.scale_factor = nz->scale_factor;
     c->nz.perm.assign(nz->perm, nz->perm + (size_t)nz->octaves * 256);
 }
+void orc_noise_eval(const orc_noise* nz, const double* xyz, double* out, size_t n) {
+    Noise N;
+    N.octaves = nz->octaves; N.frequency = nz->frequency; N.lacunarity = nz->lacunarity;
+    N.persistence = nz->persistence; N.scale_factor = nz->scale_factor;
+    N.perm.assign(nz->perm, nz->perm + (size_t)nz->octaves * 256);
+    for (size_t i = 0; i < n; ++i) out[i] = fbm3(N, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+}
 void orc_set_state(orc_ctx* c, const double* h, const double* b, const double* wh) {
     size_t N = c->g.n;
     if (h) c->h.assign(h, h + N);

@@ -51,6 +51,8 @@ void orc_destroy(orc_ctx*);
 int orc_set_inputs(orc_ctx*, const orc_inputs*);
 void orc_set_params(orc_ctx*, const orc_params*);
 void orc_set_noise(orc_ctx*, const orc_noise*);
+/* NoiseFn::get for the fBm described by nz at n points (xyz interleaved): what a host-side noise callback returns */
+void orc_noise_eval(const orc_noise* nz, const double* xyz, double* out, size_t n);
 /* overwrite the evolving state (h, b, wh) — used to start a step from a given state */
 void orc_set_state(orc_ctx*, const double* h, const double* b, const double* wh);
 /* one erode() call (erosion.rs:699); returns 0 or a negative code mirroring the panics */

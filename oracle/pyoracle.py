@@ -229,6 +229,19 @@ def get_rivers(x_lg, y_lg, scale, newh, water_alt_filled, dh, indirection, drain
     return out
 
 
+def noise_eval(nz, xyz):
+    """Fbm<Perlin>::get at the rows of xyz (n x 3): the value a host noise callback hands to the library."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+    perm = np.ascontiguousarray(nz["perm"])
+    cn = Noise(nz["octaves"], nz["frequency"], nz["lacunarity"], nz["persistence"], nz["scale_factor"], _p(perm))
+    out = np.empty(xyz.shape[0], dtype=np.float64)
+    L = lib()
+    L.orc_noise_eval.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+    L.orc_noise_eval.restype = None
+    L.orc_noise_eval(ctypes.byref(cn), _p(xyz), _p(out), xyz.shape[0])
+    return out
+
+
 def uniform_noise(values):
     """util.rs:171-207 restated in numpy: NaN = None; (1 + rank) as f32 / count as f32, ties by index."""
     v = np.asarray(values, np.float32)

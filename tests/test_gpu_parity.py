@@ -99,6 +99,28 @@ def test_newton_fallback_path_matches(monkeypatch):
         _assert_step_equal(o, c, "forced fallback step %d" % it)
 
 
+def test_host_noise_callback_matches_device_tables():
+    """ve_set_noise_cb: rock strength from a host NoiseFn.  With the callback evaluating the same fBm as
+    the device tables the steps must be bit-identical to the oracle (and hence to the table mode)."""
+    f = synth.generate(7, 7)
+    calls = []
+
+    def noise(points):
+        calls.append(points.shape)
+        return po.noise_eval(f["noise"], points)
+
+    o, c = po.Oracle(f), _ctx(f)
+    c.set_noise_callback(noise)
+    for it in range(2):
+        o.step(); c.step()
+        _assert_step_equal(o, c, "noise callback step %d" % it)
+    assert calls == [(1 << 14, 3)] * 2
+    c.set_noise_callback(None)
+    o.step(); c.step()
+    _assert_step_equal(o, c, "back to the tables")
+    assert len(calls) == 2
+
+
 def test_non_square_and_small_maps():
     for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
         f = synth.generate(x_lg, y_lg)

@@ -128,6 +128,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     memset(ctx->scratch, 0, sizeof(ctx->scratch)); memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
     memset(ctx->timers, 0, sizeof(ctx->timers));
     memset(&ctx->nz, 0, sizeof(ctx->nz));
+    ctx->noise_cb = nullptr; ctx->noise_user = nullptr; ctx->noise_host = nullptr;
     ve_default_params(&ctx->P);
     // Sweeps run one warp per node at every map size (measured: 1024^2 .. 8192^2; at 8192^2 the up-sweep
     // takes 0.53 s per step against 1.1 s with eight one-thread nodes per warp).  VE_LANES_* > 1 selects
@@ -154,6 +155,7 @@ void ve_destroy(ve_ctx* ctx) {
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
+    if (ctx->noise_host) cudaFreeHost(ctx->noise_host);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -174,6 +176,12 @@ int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz) {
     VE_CUDA(cudaMemcpy(ctx->nz.perm, nz->perm, (size_t)nz->octaves * 256, cudaMemcpyHostToDevice));
     ctx->nz.octaves = nz->octaves; ctx->nz.frequency = nz->frequency; ctx->nz.lacunarity = nz->lacunarity;
     ctx->nz.persistence = nz->persistence; ctx->nz.scale_factor = nz->scale_factor;
+    return VE_OK;
+}
+
+int ve_set_noise_cb(ve_ctx* ctx, ve_noise_cb cb, void* user) {
+    if (!ctx) return VE_ERR_INVALID;
+    ctx->noise_cb = cb; ctx->noise_user = user;
     return VE_OK;
 }
 

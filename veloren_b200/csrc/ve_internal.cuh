@@ -40,6 +40,8 @@ struct ve_ctx {
     cudaStream_t stream;
     ve_params P;
     NoiseDev nz;
+    ve_noise_cb noise_cb; void* noise_user;     // host noise callback (ve_set_noise_cb), NULL = device fBm
+    double* noise_host;                          // pinned: 3N points out, N values back (allocated on first use)
     std::string err;
     bool timing;
     uint64_t launches;

@@ -125,6 +125,23 @@ __device__ double d_perlin3(const uint8_t* p, double px, double py, double pz) {
     return fmin(1.0, fmax(-1.0, r));
 }
 
+// rock strength from the raw noise value rs = rock_strength_nz.get(p) (erosion.rs:589-603)
+__device__ __forceinline__ double max_slope_of(const ve_params& P, double rs, double wposz) {
+    const double max_angle_range = P.max_max_angle - P.min_max_angle;
+    const double logistic_2_base = vm_sqrt(3.0) * 0.63661977236758134308;
+    const double center = 0.4, dmin = center - 0.05, dmax = center + 0.05;
+    const double logit_center = vm_log(center) - vm_log1p(-center);
+    rs = fmin(1.0, fmax(-1.0, rs)) * 0.5 + 0.5;
+    double a = fmin(1.0 - 1e-7, fmax(1e-7, rs));
+    double hz = fabs(wposz / P.mountain_scale);
+    hz = fmin(dmax, fmax(dmin, hz));
+    double la = vm_log(a) - vm_log1p(-a);
+    double lh = vm_log(hz) - vm_log1p(-hz);
+    double arg = 1.0 * la + 1.0 * (lh - logit_center);
+    double rock = vm_tanh(arg / logistic_2_base) * 0.5 + 0.5;
+    return rock * max_angle_range + P.min_max_angle;
+}
+
 __global__ void __launch_bounds__(256) k_max_slope(Geom g, ve_params P, NoiseDev nz, const double* __restrict__ h,
                                                    const double* __restrict__ hscale, double* __restrict__ out,
                                                    double* __restrict__ h_t) {
@@ -133,10 +150,6 @@ __global__ void __launch_bounds__(256) k_max_slope(Geom g, ve_params P, NoiseDev
     __syncthreads();
     uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
     if (posi >= g.n) return;
-    const double max_angle_range = P.max_max_angle - P.min_max_angle;
-    const double logistic_2_base = vm_sqrt(3.0) * 0.63661977236758134308;
-    const double center = 0.4, dmin = center - 0.05, dmax = center + 0.05;
-    const double logit_center = vm_log(center) - vm_log1p(-center);
     double z = h[posi];
     h_t[posi] = z; // erosion.rs:854 h.to_vec()
     double px = (double)g.x_of(posi) * 32.0, py = (double)g.y_of(posi) * 32.0;
@@ -153,19 +166,47 @@ __global__ void __launch_bounds__(256) k_max_slope(Geom g, ve_params P, NoiseDev
         result += signal;
         px *= nz.lacunarity; py *= nz.lacunarity; pz *= nz.lacunarity;
     }
-    double rs = result * nz.scale_factor;
-    rs = fmin(1.0, fmax(-1.0, rs)) * 0.5 + 0.5;
-    double a = fmin(1.0 - 1e-7, fmax(1e-7, rs));
-    double hz = fabs(wposz / P.mountain_scale);
-    hz = fmin(dmax, fmax(dmin, hz));
-    double la = vm_log(a) - vm_log1p(-a);
-    double lh = vm_log(hz) - vm_log1p(-hz);
-    double arg = 1.0 * la + 1.0 * (lh - logit_center);
-    double rock = vm_tanh(arg / logistic_2_base) * 0.5 + 0.5;
-    out[posi] = rock * max_angle_range + P.min_max_angle;
+    out[posi] = max_slope_of(P, result * nz.scale_factor, wposz);
+}
+
+// host-callback noise (ve_set_noise_cb): sample points out, values back in
+__global__ void __launch_bounds__(256) k_noise_points(Geom g, const double* __restrict__ h, const double* __restrict__ hscale,
+                                                      double* __restrict__ xyz, double* __restrict__ h_t) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    double z = h[posi];
+    h_t[posi] = z; // erosion.rs:854 h.to_vec()
+    double wposz = z / hscale[posi];
+    double div_factor = (2.0 * 32.0) / 8.0;
+    xyz[3 * (size_t)posi] = (double)g.x_of(posi) * 32.0;
+    xyz[3 * (size_t)posi + 1] = (double)g.y_of(posi) * 32.0;
+    xyz[3 * (size_t)posi + 2] = wposz * div_factor;
+}
+__global__ void __launch_bounds__(256) k_max_slope_ext(Geom g, ve_params P, const double* __restrict__ rs, const double* __restrict__ h,
+                                                       const double* __restrict__ hscale, double* __restrict__ out) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    out[posi] = max_slope_of(P, rs[posi], h[posi] / hscale[posi]);
 }
 
 int ve_k_max_slope(ve_ctx* ctx) {
+    const size_t n = ctx->g.n;
+    if (ctx->noise_cb) {
+        double* dxyz;
+        VE_TRY(ve_scratch(ctx, 0, n * 24, (void**)&dxyz));
+        if (!ctx->noise_host) VE_CUDA(cudaMallocHost((void**)&ctx->noise_host, n * 32));
+        double* hxyz = ctx->noise_host; double* hval = ctx->noise_host + 3 * n;
+        k_noise_points<<<ve_blocks(n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->h, ctx->hscale, dxyz, ctx->h_t);
+        VE_LAUNCH_CHECK();
+        VE_CUDA(cudaMemcpyAsync(hxyz, dxyz, n * 24, cudaMemcpyDeviceToHost, ctx->stream));
+        VE_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->noise_cb(ctx->noise_user, hxyz, hval, n);
+        double* dval = dxyz;                                   // reuse the scratch for the values
+        VE_CUDA(cudaMemcpyAsync(dval, hval, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+        k_max_slope_ext<<<ve_blocks(n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->P, dval, ctx->h, ctx->hscale, ctx->max_slope);
+        VE_LAUNCH_CHECK();
+        return VE_OK;
+    }
     size_t smem = (size_t)ctx->nz.octaves * 256;
     k_max_slope<<<ve_blocks(ctx->g.n, 256), 256, smem, ctx->stream>>>(ctx->g, ctx->P, ctx->nz, ctx->h, ctx->hscale,
                                                                       ctx->max_slope, ctx->h_t);

@@ -25,7 +25,7 @@ _DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirecti
 SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
-           "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
+           "ve_set_noise_cb", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
@@ -132,6 +132,25 @@ class ErosionContext:
         nz = Noise(int(noise["octaves"]), float(noise["frequency"]), float(noise["lacunarity"]),
                    float(noise["persistence"]), float(noise["scale_factor"]), _p(perm))
         self._chk(lib().ve_set_noise(self.ctx, ctypes.byref(nz)))
+
+    def set_noise_callback(self, fn):
+        """rock_strength_nz as a host function (ve_set_noise_cb): fn(points) with points an (N, 3) float64
+        array of the `.get()` arguments (erosion.rs:585-589), returning N float64 values.  None switches
+        back to the table set with set_noise."""
+        if fn is None:
+            self._noise_cb = None
+            self._chk(lib().ve_set_noise_cb(self.ctx, None, None))
+            return
+        proto = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                 ctypes.c_size_t)
+
+        def tramp(_user, xyz, out, n):
+            pts = np.ctypeslib.as_array(xyz, shape=(n, 3))
+            res = np.ctypeslib.as_array(out, shape=(n,))
+            res[:] = np.asarray(fn(pts), dtype=np.float64).reshape(n)
+
+        self._noise_cb = proto(tramp)                      # keep the trampoline alive
+        self._chk(lib().ve_set_noise_cb(self.ctx, self._noise_cb, None))
 
     def set_inputs(self, fields):
         spec = dict(oldh=np.float32, oldb=np.float32, is_ocean=np.uint8, uplift=np.float32, n=np.float32,
