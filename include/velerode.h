@@ -161,6 +161,8 @@ int ve_get_rivers(ve_ctx* ctx, double continent_scale_hack, const uint32_t* newh
  * uniform_noise (util.rs:171-207): values[i] = the sample, NaN = None; cdf[i] = (1 + rank) / count as f32
  * with ties broken by index, 0 for None. */
 int ve_uniform_noise(ve_ctx* ctx, const float* values, float* cdf);
+/* map_edge_factor (util.rs:22-29) for every chunk, f32. */
+int ve_map_edge_factor(ve_ctx* ctx, float* out);
 /* get_horizon_map (util.rs:371-449) for bounds = the whole map, F = f32: raw slope ("angle" before
  * to_angle) and occluder height (before to_height) for the west and the east march. */
 int ve_horizon_map(ve_ctx* ctx, float minh, float maxh, const float* h, float* west_angle, float* west_height,

@@ -242,6 +242,16 @@ def noise_eval(nz, xyz):
     return out
 
 
+def map_edge_factor(x_lg, y_lg):
+    """util.rs:22-29 restated in numpy (f32 arithmetic)."""
+    sx, sy = 1 << x_lg, 1 << y_lg
+    ex = np.arange(sx, dtype=np.int64)[None, :].repeat(sy, 0)
+    ey = np.arange(sy, dtype=np.int64)[:, None].repeat(sx, 1)
+    fx = (sx // 2 - np.abs(ex - sx // 2)).astype(np.float32) / (np.float32(16.0) / np.float32(1024.0) * np.float32(sx))
+    fy = (sy // 2 - np.abs(ey - sy // 2)).astype(np.float32) / (np.float32(16.0) / np.float32(1024.0) * np.float32(sy))
+    return np.clip(np.minimum(fx, fy), np.float32(0), np.float32(1)).astype(np.float32).ravel()
+
+
 def uniform_noise(values):
     """util.rs:171-207 restated in numpy: NaN = None; (1 + rank) as f32 / count as f32, ties by index."""
     v = np.asarray(values, np.float32)

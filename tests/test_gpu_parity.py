@@ -256,6 +256,12 @@ def test_errors_are_reported_not_swallowed():
         ErosionContext(1, 1)
 
 
+def test_map_edge_factor():
+    for x_lg, y_lg in ((7, 7), (6, 9), (10, 10)):
+        c = ErosionContext(x_lg, y_lg)
+        assert bit_diff(po.map_edge_factor(x_lg, y_lg), c.map_edge_factor()) == 0
+
+
 def test_uniform_noise_and_horizon_map():
     """rank CDF (util.rs:171-207) and the horizon ray march (util.rs:371-449)."""
     lg = 6

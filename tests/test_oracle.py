@@ -219,3 +219,12 @@ def test_uniform_noise_restated():
     v = np.array([0.5, np.nan, -1.0, 0.5, 2.0], np.float32)
     out = po.uniform_noise(v)
     assert np.array_equal(out, np.array([2, 0, 1, 3, 4], np.float32) / np.float32(4))
+
+
+def test_map_edge_factor_restatement():
+    """util.rs:22-29: hand-checked values (1024 chunks: 16 chunks = 1.0; the far edge is one chunk short)."""
+    m = po.map_edge_factor(10, 10).reshape(1024, 1024)
+    assert m[0, 0] == 0.0 and m[8, 8] == np.float32(0.5) and m[16, 500] == 1.0 and m[512, 512] == 1.0
+    assert m[1023, 3] == np.float32(1.0 / 16.0) and m[3, 1023] == np.float32(1.0 / 16.0)
+    r = po.map_edge_factor(6, 9).reshape(512, 64)          # non-square: x decides near the x edges
+    assert r[256, 0] == 0.0 and r[256, 1] == np.float32(1.0) and r[4, 32] == np.float32(0.5)

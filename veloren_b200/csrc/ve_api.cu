@@ -512,6 +512,29 @@ int ve_uniform_noise(ve_ctx* ctx, const float* values, float* cdf) {
     return VE_OK;
 }
 
+// util.rs:22-29: distance to the nearest map edge in units of 1/64 of the side, clamped to [0, 1], f32 arithmetic
+__global__ void __launch_bounds__(256) k_map_edge_factor(Geom g, float* __restrict__ out) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    int ex = g.x_of(posi), ey = g.y_of(posi);
+    int sx = g.nx, sy = g.ny;
+    float fx = (float)(sx / 2 - abs(ex - sx / 2)) / ((16.0f / 1024.0f) * (float)sx);
+    float fy = (float)(sy / 2 - abs(ey - sy / 2)) / ((16.0f / 1024.0f) * (float)sy);
+    out[posi] = fminf(fmaxf(fminf(fx, fy), 0.0f), 1.0f);
+}
+
+int ve_map_edge_factor(ve_ctx* ctx, float* out) {
+    if (!ctx || !out) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    size_t n = ctx->g.n;
+    float* d = (float*)ctx->elev;
+    k_map_edge_factor<<<ve_blocks(n, 256), 256, 0, ctx->stream>>>(ctx->g, d);
+    VE_LAUNCH_CHECK();
+    VE_CUDA(cudaMemcpyAsync(out, d, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return VE_OK;
+}
+
 int ve_horizon_map(ve_ctx* ctx, float minh, float maxh, const float* h, float* west_angle, float* west_height,
                    float* east_angle, float* east_height) {
     if (!ctx || !h || !west_angle || !west_height || !east_angle || !east_height) return VE_ERR_INVALID;

@@ -29,7 +29,7 @@ EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_
            "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
-           "ve_horizon_map"]
+           "ve_map_edge_factor", "ve_horizon_map"]
 
 
 class VeError(RuntimeError):
@@ -284,6 +284,11 @@ class ErosionContext:
         v = np.ascontiguousarray(values, np.float32)
         out = np.empty(self.n, np.float32)
         self._chk(lib().ve_uniform_noise(self.ctx, _p(v), _p(out)))
+        return out
+
+    def map_edge_factor(self):
+        out = np.empty(self.n, np.float32)
+        self._chk(lib().ve_map_edge_factor(self.ctx, _p(out)))
         return out
 
     def horizon_map(self, minh, maxh, h):
