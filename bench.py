@@ -30,7 +30,7 @@ X_LG = Y_LG = 10
 G4_BYTES_PER_CELL = 145
 FIXED_BYTES_PER_CELL, GS_BYTES_PER_CELL = 684, 374
 # dram__bytes_read.sum + dram__bytes_write.sum of one up-sweep launch (ncu --set full, round 1)
-NCU_TRAFFIC_BYTES = 146554624 + 30180864
+NCU_TRAFFIC_BYTES = 146022144 + 30922240
 
 
 def peaks():
@@ -167,7 +167,7 @@ def run_ours(args):
     achieved = G4_BYTES_PER_CELL * n / per_launch / 1e9
     roofline = {"bound": "hbm", "kernel": "k_sweep_warp<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
                 "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r01d_ncu_full_OpGsUp.txt (dram read 146.55 MB + write 30.18 MB per launch)", "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
+                "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r01g_ncu_full_OpGsUp.txt (dram read 146.02 MB + write 30.92 MB per launch)", "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
                 "n_gs_per_step": gs_counts}
 
     # ---- e2e: public call with host buffers (pinned), H2D inputs + K steps + D2H results -----
