@@ -121,6 +121,17 @@ def test_host_noise_callback_matches_device_tables():
     assert len(calls) == 2
 
 
+def test_lake_water_volume_replay_mid_loop(monkeypatch):
+    """lake_water_volume updates are logged and replayed once after the Gauss-Seidel loop; a full log is
+    replayed earlier.  VE_LWV_SMALL_LOG forces a replay before every iteration (plateau: many lakes)."""
+    monkeypatch.setenv("VE_LWV_SMALL_LOG", "1")
+    f = synth.generate(7, 7, kind=1)
+    o, c = po.Oracle(f), _ctx(f)
+    for it in range(3):
+        o.step(); c.step()
+        _assert_step_equal(o, c, "small lwv log step %d" % it)
+
+
 def test_non_square_and_small_maps():
     for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
         f = synth.generate(x_lg, y_lg)
