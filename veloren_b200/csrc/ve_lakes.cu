@@ -45,14 +45,22 @@ __global__ void __launch_bounds__(256) k_root_jump(uint32_t n, uint32_t* root, i
 __global__ void __launch_bounds__(256) k_lake_stats(uint32_t n, const int32_t* __restrict__ dh, const uint32_t* __restrict__ root,
                                                     const double* __restrict__ h, uint32_t* __restrict__ size,
                                                     unsigned long long* __restrict__ maxh_bits, uint32_t* __restrict__ counts) {
+    // warp-aggregated: a million atomics on the same three words took 0.7 ms
+    const unsigned full = 0xffffffffu;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    atomicAdd(size + root[i], 1u);
-    unsigned long long hb = (unsigned long long)__double_as_longlong(fabs(h[i])); // non-negative: bits are monotone
-    atomicMax(maxh_bits, hb);
-    int32_t d = dh[i];
-    if (d == -2) atomicAdd(counts + 0, 1u);
-    else if (d == -1) atomicAdd(counts + 1, 1u);
+    const bool in = i < n;
+    if (in) atomicAdd(size + root[i], 1u);
+    unsigned long long hb = in ? (unsigned long long)__double_as_longlong(fabs(h[i])) : 0ull; // non-negative: bits are monotone
+    uint32_t hi = (uint32_t)(hb >> 32), lo = (uint32_t)hb;
+    uint32_t mhi = __reduce_max_sync(full, hi);
+    uint32_t mlo = __reduce_max_sync(full, hi == mhi ? lo : 0u);
+    int32_t d = in ? dh[i] : 0;
+    unsigned c2 = __popc(__ballot_sync(full, in && d == -2)), c1 = __popc(__ballot_sync(full, in && d == -1));
+    if ((threadIdx.x & 31u) == 0u) {
+        atomicMax(maxh_bits, ((unsigned long long)mhi << 32) | mlo);
+        if (c2) atomicAdd(counts + 0, c2);
+        if (c1) atomicAdd(counts + 1, c1);
+    }
 }
 // Euler tour of the dh forest (children in ascending slot); every tree ends with END.
 __global__ void __launch_bounds__(256) k_tree_arcs(Geom g, const int32_t* __restrict__ dh, uint32_t* __restrict__ succ,
