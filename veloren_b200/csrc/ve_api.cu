@@ -109,7 +109,7 @@ static int create_impl(ve_ctx* ctx, uint32_t x_lg, uint32_t y_lg, const int* dev
     VE_TRY(dev_alloc(ctx, &ctx->b_spl, n)); VE_TRY(dev_alloc(ctx, &ctx->wh_mrec, n)); VE_TRY(dev_alloc(ctx, &ctx->h_pre_diff, n));
     VE_TRY(dev_alloc(ctx, &ctx->kfs, n * 8)); VE_TRY(dev_alloc(ctx, &ctx->kdf, n * 8));
     VE_TRY(dev_alloc(ctx, &ctx->sill_cur, n)); VE_TRY(dev_alloc(ctx, &ctx->sill_prev, n));
-    VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->order_bu, n)); VE_TRY(dev_alloc(ctx, &ctx->level, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
+    VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->order_bu, n)); VE_TRY(dev_alloc(ctx, &ctx->level, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->don_live, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_parent, n)); VE_TRY(dev_alloc(ctx, &ctx->f_jump, n)); VE_TRY(dev_alloc(ctx, &ctx->f_depth, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_root, n));
     VE_TRY(dev_alloc(ctx, &ctx->abort_word, 64));
@@ -150,7 +150,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->mrec, ctx->ndon, ctx->mwrec, ctx->area, ctx->max_slope, ctx->kd_eff, ctx->h_t, ctx->h_new,
                     ctx->deltah, ctx->elev, ctx->h_p, ctx->lake_silt, ctx->lwv, ctx->wh_prev, ctx->h_spl, ctx->b_spl,
                     ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td, ctx->order_bu, ctx->level,
-                    ctx->don_order, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
+                    ctx->don_order, ctx->don_live, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
