@@ -199,7 +199,25 @@ int get_lakes(const Grid& g, const double* h, int32_t* downhill_, int32_t* indir
         }
     }
 
+    // test/debug aid (ORC_DUMP_LAKES=<file>): the directed pass table as the growth phase sees it, then the
+    // connections in the order they are made.  Used by tools/lake_growth_prototype.py.
+    FILE* dumpf = nullptr;
+    if (const char* dp = getenv("ORC_DUMP_LAKES")) dumpf = fopen(dp, "wb");
+    if (dumpf) {
+        std::vector<int64_t> rec;
+        for (size_t e = 0; e < lakes.size(); ++e) {
+            const Pass& edge = lakes[e];
+            if (edge.from == -1) continue;
+            int32_t ii = indirection[edge.from]; size_t lf = ii < 0 ? (size_t)edge.from : (size_t)ii;
+            ii = indirection[edge.to]; size_t lt = ii < 0 ? (size_t)edge.to : (size_t)ii;
+            rec.push_back(edge.from); rec.push_back(edge.to); rec.push_back((int64_t)lf); rec.push_back((int64_t)lt);
+            rec.push_back(downhill_[lt] == -2 ? 1 : 0);
+        }
+        int64_t cnt = (int64_t)(rec.size() / 5);
+        fwrite(&cnt, 8, 1, dumpf); fwrite(rec.data(), 8, rec.size(), dumpf);
+    }
     std::vector<size_t> pass_flows_sorted;
+    std::vector<int64_t> dump_conn;
     // 2076-2137
     while (!candidates.empty()) {
         Cand c = candidates.top(); candidates.pop();
@@ -214,6 +232,7 @@ int get_lakes(const Grid& g, const double* h, int32_t* downhill_, int32_t* indir
         downhill_[lake_chunk_idx] = (int32_t)neighbor_idx;
         indirection[lake_chunk_idx] = -(int32_t)chunk_idx;
         pass_flows_sorted.push_back(lake_chunk_idx);
+        if (dumpf) { dump_conn.push_back((int64_t)lake_chunk_idx); dump_conn.push_back(chunk_idx); dump_conn.push_back(neighbor_idx); }
         for (size_t s = lake_idx; s < lake_idx + max_len; ++s) {
             Pass& edge_ref = lakes[s];
             if (edge_ref.from == (int32_t)chunk_idx && edge_ref.to == neighbor_idx) continue;
@@ -228,6 +247,11 @@ int get_lakes(const Grid& g, const double* h, int32_t* downhill_, int32_t* indir
         }
     }
 
+    if (dumpf) {
+        int64_t cnt = (int64_t)(dump_conn.size() / 3);
+        fwrite(&cnt, 8, 1, dumpf); fwrite(dump_conn.data(), 8, dump_conn.size(), dumpf);
+        fclose(dumpf);
+    }
     // 2141-2290: re-route flooded cells of each lake, then final BFS order.
     enum : uint8_t { UnParsed = 0, InQueue = 1, WithRcv = 2 };
     std::vector<uint8_t> tag(N, UnParsed);
