@@ -291,13 +291,13 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                     const uint32_t ci = cb + (uint32_t)(bal ? (__ffs(bal) - 1) : 0);
                     c0 = ((uint64_t)m0r << 32) | m1r; c1 = ((uint64_t)m2r << 32) | m3r;
                     if (!key_less(c0, c1, l0, l1)) break;
+                    // no barrier needed: every lane makes every store itself, so what a lane reads later
+                    // is either its own store or one by lane 0 in the push path, which ends with a barrier
                     uint4 pl = s2[ci];
-                    __syncwarp();
                     s0[i] = c0; s1[i] = c1; s2[i] = pl;
-                    __syncwarp();
                     i = ci;
                 }
-                if (i != hn) { uint4 pl = s2[hn]; __syncwarp(); s0[i] = l0; s1[i] = l1; s2[i] = pl; }
+                if (i != hn) { uint4 pl = s2[hn]; s0[i] = l0; s1[i] = l1; s2[i] = pl; }
                 __syncwarp();
             } else {
             for (;;) { // sift down: the 32 children of i are scanned by the lanes
@@ -367,7 +367,20 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                 uint4 pp;
                 pp.x = __shfl_sync(0xffffffffu, pl.x, src); pp.y = __shfl_sync(0xffffffffu, pl.y, src);
                 pp.z = __shfl_sync(0xffffffffu, pl.z, src); pp.w = __shfl_sync(0xffffffffu, pl.w, src);
-                if (lane == 0) { // sift up
+                if (hn < heap_smem) {
+                    // shared-memory heap: sift up in every lane alike (see the sift-down above)
+                    best0[pp.x] = p0; best1[pp.x] = p1;   // ok => this candidate beats the lake's best so far
+                    uint32_t i = hn;
+                    while (i > 0) {
+                        uint32_t pi = (i - 1u) / 32u;
+                        uint64_t q0 = s0[pi], q1 = s1[pi];
+                        if (!key_less(p0, p1, q0, q1)) break;
+                        uint4 pl2 = s2[pi];
+                        s0[i] = q0; s1[i] = q1; s2[i] = pl2;
+                        i = pi;
+                    }
+                    s0[i] = p0; s1[i] = p1; s2[i] = pp;
+                } else if (lane == 0) { // sift up
                     best0[pp.x] = p0; best1[pp.x] = p1;   // ok => this candidate beats the lake's best so far
                     uint32_t i = hn;
                     while (i > 0) {
