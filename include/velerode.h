@@ -81,17 +81,26 @@ typedef enum {
 /* Scalars of the last step (ve_get_scalar). */
 typedef enum {
     VE_S_N_GS = 0, VE_S_ERR, VE_S_MAXH, VE_S_BOUNDARY_LEN, VE_S_N_LAKES, VE_S_MAX_UPLIFT, VE_S_MAX_G,
-    VE_S_N_UNDERWATER
+    VE_S_N_UNDERWATER,
+    VE_S_UP_MS_TOTAL,        /* device milliseconds spent in up-sweep launches since ve_create (CUDA events) */
+    VE_S_UP_LAUNCHES_TOTAL   /* number of up-sweep launches since ve_create */
 } ve_scalar;
 
 void ve_default_params(ve_params* p);
 /* One context per map and per calling thread (batch_generate runs several worlds on
  * independent threads, world/examples/batch_generate.rs:287-352).  device_ids/n_devices:
- * GPUs to use; round 1 uses device_ids[0] (NULL -> current device). */
+ * GPUs to use; the context lives on device_ids[0] (NULL -> current device); one map is not split across
+ * GPUs, several contexts on several devices may be used from one process. */
 int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids, int n_devices);
 void ve_destroy(ve_ctx* ctx);
 const char* ve_last_error(ve_ctx* ctx);
 
+/* Test and tuning knobs (no counterpart in the reference; defaults are what production uses).  Keys:
+ * "lanes_up" / "lanes_down" / "lanes_other" (k > 1: thread-per-node sweeps), "df_bps" (resident blocks per SM
+ * of the sweeps), "newton" (bit 0: skip the Newton loop, bit 2: force the slow re-solve), "newton_variant",
+ * "lwv_small_log", "thermal_sweep", "lakes_trace", "serial_err" (always sum the Gauss-Seidel error in the
+ * reference's serial order), "spin_limit_ms" (give-up time of a stalled sweep). */
+int ve_set_debug(ve_ctx* ctx, const char* key, long long value);
 int ve_set_params(ve_ctx* ctx, const ve_params* p);
 int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz);
 /* Alternative rock-strength source for get_max_slope (erosion.rs:550-604): the host's own
@@ -126,6 +135,9 @@ double ve_get_scalar(ve_ctx* ctx, int which);
 /* number of kernels launched by this context so far, and seconds spent per stage of the last
  * step (names via ve_timer_name) when ve_set_timing(ctx, 1) is on (adds synchronisations). */
 uint64_t ve_launch_count(ve_ctx* ctx);
+/* Gauss-Seidel iteration count and lake count of the last `cap` erode() steps (oldest first); returns how
+ * many entries were written (at most 256 are kept). */
+int ve_get_history(ve_ctx* ctx, int32_t* n_gs, uint32_t* n_lakes, int cap);
 int ve_set_timing(ve_ctx* ctx, int on);
 int ve_get_timers(ve_ctx* ctx, double* dst, int cap);
 const char* ve_timer_name(int i);
@@ -137,6 +149,9 @@ int ve_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh /*in-out*/, int32_t* 
                  uint32_t* newh, double* maxh, uint64_t* boundary_len);                /* erosion.rs:1825 */
 int ve_get_multi_rec(ve_ctx* ctx, const double* h, const int32_t* dh, const uint32_t* newh,
                      double* wh /*in-out*/, uint8_t* mrec, uint32_t* mstack, double* mwrec); /* 2332 */
+/* A pure function of its three inputs, like the reference's: the donor lists are rebuilt from mrec and the
+ * positions in mstack, the area is gathered along mstack.  An mstack in which a receiver precedes one of its
+ * donors (the reference would silently produce nonsense) returns VE_ERR_STACK_INCOMPLETE. */
 int ve_get_multi_drainage(ve_ctx* ctx, const uint32_t* mstack, const uint8_t* mrec,
                           const double* mwrec, double* area);                          /* erosion.rs:62 */
 int ve_fill_sinks(ve_ctx* ctx, const double* h, const uint8_t* is_ocean, double* out); /* erosion.rs:1738 */
@@ -173,7 +188,9 @@ int ve_horizon_map(ve_ctx* ctx, float minh, float maxh, const float* h, float* w
  * limits): d_h, d_b, d_kd_eff are DEVICE pointers owned by the caller (N doubles each, h and b
  * updated in place) and the solver's work space is an array built into the library
  * (6 MiB per GPU, held until exit), so maps are limited to 512x512 cells; larger ones return
- * VE_ERR_TOO_LARGE with a message in errbuf.  Calls nothing that allocates.  The first call on a
+ * VE_ERR_TOO_LARGE with a message in errbuf.  Calls nothing that allocates (the one 4-byte status word it
+ * reads back at the end goes through the driver's own staging buffer into a stack variable: a synchronous
+ * copy, no allocation).  The first call on a
  * device looks the array's device address up: issue it before any stream capture.  All calls on a
  * device share the array, so calls that overlap on the GPU race; serialise them.  cuda_stream: a
  * cudaStream_t (NULL = default stream); the call returns after the work has finished. */

@@ -48,13 +48,14 @@ Grid make_grid(uint32_t xlg, uint32_t ylg) {
 }
 
 struct Math {
-    bool libm;
+    bool libm;    // f64 transcendentals from the host libm instead of ve_exact_math.h
+    bool libmf;   // f32 powf(dh, 0.5) of the Newton loop from the host libm's powf instead of sqrtf
     inline double pow_(double x, double y) const { return libm ? std::pow(x, y) : vm_pow(x, y); }
     inline double exp_(double x) const { return libm ? std::exp(x) : vm_exp(x); }
     inline double log_(double x) const { return libm ? std::log(x) : vm_log(x); }
     inline double log1p_(double x) const { return libm ? std::log1p(x) : vm_log1p(x); }
     inline double tanh_(double x) const { return libm ? std::tanh(x) : vm_tanh(x); }
-    inline float powf_(float x, float y) const { return libm ? std::pow(x, y) : vm_powf(x, y); }
+    inline float powf_(float x, float y) const { return libmf ? std::pow(x, y) : vm_powf(x, y); }
 };
 
 double now_s() {
@@ -730,7 +731,7 @@ void orc_set_state(orc_ctx* c, const double* h, const double* b, const double* w
 // erosion.rs:699-1731  erode
 int orc_step(orc_ctx* c) {
     const Grid& g = c->g; const size_t N = g.n; const orc_params& P = c->P;
-    Math M; M.libm = P.use_libm != 0;
+    Math M; M.libm = (P.use_libm & 1) != 0; M.libmf = (P.use_libm & 2) != 0;
 #ifdef _OPENMP
     if (P.n_threads > 0) omp_set_num_threads(P.n_threads);
 #endif
@@ -1205,7 +1206,7 @@ int orc_get_lakes(uint32_t x_lg, uint32_t y_lg, const double* h, int32_t* dh, in
 }
 void orc_get_multi_rec(uint32_t x_lg, uint32_t y_lg, const double* h, const int32_t* dh, const uint32_t* newh,
                        double* wh, uint8_t* mrec, uint32_t* mstack, double* mwrec, int use_libm) {
-    Math M; M.libm = use_libm != 0;
+    Math M; M.libm = (use_libm & 1) != 0; M.libmf = (use_libm & 2) != 0;
     get_multi_rec(make_grid(x_lg, y_lg), M, h, dh, newh, wh, mrec, mstack, mwrec, 32.0, 32.0, nullptr);
 }
 void orc_get_multi_drainage(uint32_t x_lg, uint32_t y_lg, const uint32_t* mstack, const uint8_t* mrec,
@@ -1275,7 +1276,7 @@ void orc_water_alt(uint32_t x_lg, uint32_t y_lg, const double* alt, const uint8_
 int orc_get_rivers(uint32_t x_lg, uint32_t y_lg, double continent_scale_hack, const uint32_t* newh, const double* water_alt,
                    const int32_t* downhill_, const int32_t* indirection, const double* drainage, orc_river* rivers, int use_libm) {
     Grid g = make_grid(x_lg, y_lg);
-    Math M; M.libm = use_libm != 0;
+    Math M; M.libm = (use_libm & 1) != 0; M.libmf = (use_libm & 2) != 0;
     const double rainfall_chunk_rate = (double)(1.0f / (512.0f * 32.0f * 32.0f));   // config.rs:73
     const double river_roughness = (double)0.06125f, river_max_width = (double)2.0f, river_min_height = (double)0.25f,
                  river_width_to_depth = (double)8.0f;                                  // config.rs:74-77

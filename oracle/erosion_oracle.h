@@ -29,7 +29,9 @@ typedef struct {
     double chunk_area_pow_q;   /* 1024^0.2 (erosion.rs:926) */
     double min_max_angle, max_max_angle, mid_slope; /* tan 15/60/30 deg (556-557, 863) */
     double mountain_scale;     /* CONFIG.mountain_scale = 2048 (config.rs:62) */
-    int use_libm;              /* 1: glibc libm instead of ve_exact_math.h (deviation study) */
+    int use_libm;              /* deviation study, bit mask: 1 = f64 pow/exp/ln/ln_1p/tanh from glibc instead of
+                                  ve_exact_math.h; 2 = the f32 powf(dh, 0.5) of the Newton loop from glibc's powf
+                                  instead of sqrtf (erosion.rs:1343-1347) */
     int n_threads;             /* 0: omp default */
 } orc_params;
 

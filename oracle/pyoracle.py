@@ -66,7 +66,9 @@ def _p(a):
 class Oracle:
     """One map's erosion state on the CPU; mirrors the ve_* C-ABI so tests read the same."""
 
-    def __init__(self, fields, use_libm=False, n_threads=0):
+    def __init__(self, fields, use_libm=False, n_threads=0, libm_f32_powf=None):
+        # use_libm: f64 transcendentals from glibc; libm_f32_powf: the Newton loop's powf(dh, 0.5) from glibc's
+        # powf (default: follows use_libm, the round-1 meaning of the switch)
         L = lib()
         self.x_lg, self.y_lg = fields["x_lg"], fields["y_lg"]
         self.n = (1 << self.x_lg) * (1 << self.y_lg)
@@ -78,7 +80,7 @@ class Oracle:
         L.orc_default_params(ctypes.byref(prm))
         prm.k_d_scale = fields["k_d_scale"]
         prm.k_da = fields["k_da"]
-        prm.use_libm = int(use_libm)
+        prm.use_libm = (1 if use_libm else 0) | (2 if (use_libm if libm_f32_powf is None else libm_f32_powf) else 0)
         prm.n_threads = int(n_threads)
         L.orc_set_params(self.ctx, ctypes.byref(prm))
         nz = fields["noise"]

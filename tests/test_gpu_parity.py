@@ -71,32 +71,36 @@ def test_c5_plateau_256_lake_heavy():
         _assert_step_equal(o, c, "C5 step %d" % it)
 
 
-def test_thread_per_node_sweeps_match_too(monkeypatch):
-    """Maps beyond 4096^2 run the sweeps with several nodes per warp (one thread per node) instead of
-    one warp per node; force that path on a small map (the lane counts are read at ve_create)."""
-    for k in ("VE_LANES_UP", "VE_LANES_DOWN", "VE_LANES_OTHER"):
-        monkeypatch.setenv(k, "8")
+def test_thread_per_node_sweeps_match_too():
+    """The sweeps can also run several nodes per warp (one thread per node) instead of one warp per node
+    (kept for comparison); force that path on a small map through the debug setter."""
     f = synth.generate(7, 7)
     o, c = po.Oracle(f), _ctx(f)
+    c.set_debug(lanes_up=8, lanes_down=8, lanes_other=8)
     for it in range(3):
         o.step(); c.step()
         _assert_step_equal(o, c, "lanes=8 step %d" % it)
     g = synth.generate(7, 7, kind=1)
     o, c = po.Oracle(g), _ctx(g)
+    c.set_debug(lanes_up=8, lanes_down=8, lanes_other=8)
     for it in range(2):
         o.step(); c.step()
         _assert_step_equal(o, c, "lanes=8 plateau step %d" % it)
 
 
-def test_newton_fallback_path_matches(monkeypatch):
-    """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with
-    the plain operators if a range test ever failed; VE_DBG=4 forces the second solve for every node."""
-    monkeypatch.setenv("VE_DBG", "4")
+@pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1)])
+def test_alternative_code_paths_match(knob):
+    """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with the
+    plain operators if a range test ever failed: newton=4 forces the second solve for every node,
+    newton_variant selects another formulation of the Newton loop; serial_err=1 sums the Gauss-Seidel error in
+    the reference's serial order every iteration (normally only when it lands within rounding of the
+    tolerance); thermal_sweep=1 the ordered sweep of erosion.rs:1620 instead of pointer jumping."""
     f = synth.generate(7, 7)
     o, c = po.Oracle(f), _ctx(f)
+    c.set_debug(**knob)
     for it in range(3):
         o.step(); c.step()
-        _assert_step_equal(o, c, "forced fallback step %d" % it)
+        _assert_step_equal(o, c, "%s step %d" % (knob, it))
 
 
 def test_host_noise_callback_matches_device_tables():
@@ -119,14 +123,22 @@ def test_host_noise_callback_matches_device_tables():
     o.step(); c.step()
     _assert_step_equal(o, c, "back to the tables")
     assert len(calls) == 2
+    # callback only: no device table was ever uploaded (ve_set_noise not called)
+    c2 = ErosionContext(7, 7)
+    c2.set_params(k_d_scale=f["k_d_scale"], k_da=f["k_da"])
+    c2.set_inputs(f)
+    c2.set_noise_callback(noise)
+    o2 = po.Oracle(f)
+    o2.step(); c2.step()
+    _assert_step_equal(o2, c2, "callback-only context")
 
 
-def test_lake_water_volume_replay_mid_loop(monkeypatch):
+def test_lake_water_volume_replay_mid_loop():
     """lake_water_volume updates are logged and replayed once after the Gauss-Seidel loop; a full log is
-    replayed earlier.  VE_LWV_SMALL_LOG forces a replay before every iteration (plateau: many lakes)."""
-    monkeypatch.setenv("VE_LWV_SMALL_LOG", "1")
+    replayed earlier.  lwv_small_log forces a replay before every iteration (plateau: many lakes)."""
     f = synth.generate(7, 7, kind=1)
     o, c = po.Oracle(f), _ctx(f)
+    c.set_debug(lwv_small_log=1)
     for it in range(3):
         o.step(); c.step()
         _assert_step_equal(o, c, "small lwv log step %d" % it)
@@ -265,6 +277,66 @@ def test_errors_are_reported_not_swallowed():
         c.step()            # no inputs/noise configured
     with pytest.raises(Exception):
         ErosionContext(1, 1)
+    with pytest.raises(VeError):
+        c.set_debug(no_such_knob=1)
+
+
+def test_error_codes_mirror_the_reference_panics():
+    """assert_ne!(bet, 0.0) (diffusion.rs:445) -> VE_ERR_TRIDAG_SINGULAR; panic!("Disconnected lake!")
+    (erosion.rs:1251) -> VE_ERR_DISCONNECTED_LAKE; an order that is not topological (the reference's
+    assert_eq!(stack.len(), nn), erosion.rs:2510, can never pass such an order on) -> the sweep gives up
+    with VE_ERR_STACK_INCOMPLETE instead of hanging the device."""
+    lg = 5
+    n = 1 << (2 * lg)
+    c = ErosionContext(lg, lg)
+    rng = np.random.default_rng(3)
+    h = rng.random(n) * 10.0
+    # dt/2/dx^2 = 1 and kd = -0.5 everywhere: diag = 1 + (-0.5) + (-0.5) == 0 at the first interior element
+    with pytest.raises(VeError) as ei:
+        c.diffusion(2048.0, h, h - 1.0, np.full(n, -0.5))
+    assert ei.value.code == -4
+    # no ocean cell at all: every local minimum is a -1 lake and none can reach the boundary
+    dh = c.downhill(h, np.zeros(n, np.uint8))
+    assert (dh == -1).any() and not (dh == -2).any()
+    with pytest.raises(VeError) as ei:
+        c.get_lakes(h, dh)
+    assert ei.value.code == -3
+    # get_multi_drainage is a pure function of its inputs ...
+    f = synth.generate(lg, lg)
+    o = po.Oracle(f); o.step()
+    mstack, mrec, mwrec = o.get("mstack"), o.get("mrec"), o.get("mwrec")
+    assert bit_diff(c.get_multi_drainage(mstack, mrec, mwrec), o.get("area")) == 0
+    # ... and an mstack in which a node depends on one that never appears (its receiver's entry replaced by a
+    # duplicate) stalls the gather, which gives up instead of hanging
+    bad = mstack.copy()
+    has_don = np.flatnonzero(mrec != 0)
+    victim = int(has_don[0])                             # a node with receivers: it is some receiver's donor
+    pos = int(np.flatnonzero(mstack == victim)[0])
+    bad[pos] = mstack[0] if pos != 0 else mstack[1]      # victim never published
+    c.set_debug(spin_limit_ms=300)
+    with pytest.raises(VeError) as ei:
+        c.get_multi_drainage(bad, mrec, mwrec)
+    assert ei.value.code == -5
+    c.set_debug(spin_limit_ms=0)
+    assert bit_diff(c.get_multi_drainage(mstack, mrec, mwrec), o.get("area")) == 0      # the context is usable again
+
+
+def test_two_contexts_on_two_devices_in_one_process():
+    """Function attributes (the >48 KB shared-memory opt-ins) and occupancy are per device: stepping contexts on
+    two GPUs from one process must work (skipped on a single-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    f = synth.generate(7, 7, kind=1)
+    o = po.Oracle(f)
+    cs = [ErosionContext(7, 7, device=d) for d in (0, 1)]
+    for c in cs:
+        c.configure(f)
+    for it in range(2):
+        o.step()
+        for c in cs:
+            c.step()
+            _assert_step_equal(o, c, "device ctx step %d" % it)
 
 
 def test_map_edge_factor():

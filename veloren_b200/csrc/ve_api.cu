@@ -4,6 +4,8 @@
 #include <string.h>
 #include <chrono>
 #include <stdlib.h>
+#include <mutex>
+#include <nvtx3/nvToolsExt.h>
 
 static const char* TIMER_NAMES[VT_COUNT] = {"downhill", "get_lakes", "wh_fill", "mrec", "stack", "area", "max_slope",
                                             "k_factors", "gs_down", "gs_up", "gs_lwv", "basement", "thermal",
@@ -30,6 +32,31 @@ int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out) {
     *out = ctx->cub_tmp;
     return VE_OK;
 }
+// Function attributes are per device and the occupancy depends on them: the opt-in is made under a mutex
+// for the device that is current, the occupancy is cached per context (contexts may live on different
+// devices and run on different host threads).
+static std::mutex g_attr_mu;
+int ve_occupancy(ve_ctx* ctx, const void* func, int block, size_t smem, int* bps_out) {
+    auto it = ctx->occ_cache.find(func);
+    if (it != ctx->occ_cache.end() && it->second.second == smem) { *bps_out = it->second.first; return VE_OK; }
+    if (smem > 48 * 1024) {
+        std::lock_guard<std::mutex> lk(g_attr_mu);
+        VE_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    int bps = 0;
+    VE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, func, block, smem));
+    if (bps < 1) { ctx->err = "kernel does not fit an SM"; return VE_ERR_CUDA; }
+    ctx->occ_cache[func] = std::make_pair(bps, smem);
+    *bps_out = bps;
+    return VE_OK;
+}
+// A polling worker gives up after this long: a legitimately waiting node can wait for most of a sweep
+// (~1 s at 8192^2), so the limit scales with the map.
+uint64_t ve_spin_limit_ns(const ve_ctx* ctx) {
+    if (ctx->spin_limit_ns) return ctx->spin_limit_ns;
+    return 5000000000ull + (uint64_t)ctx->g.n * 200ull;
+}
+
 int ve_check_abort(ve_ctx* ctx) {
     uint32_t a = 0;
     VE_CUDA(cudaMemcpyAsync(&a, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -37,7 +64,8 @@ int ve_check_abort(ve_ctx* ctx) {
     ctx->df_pending = 0;
     if (a) {
         cudaMemsetAsync(ctx->abort_word, 0, 4, ctx->stream);
-        ctx->err = "dataflow sweep stalled: order is not topological (stack/newh incomplete)";
+        ctx->err = "dataflow sweep stalled: order is not topological (stack/newh incomplete); the context's step state is undefined, "
+                   "reload it with ve_set_inputs / ve_set_state";
         return VE_ERR_STACK_INCOMPLETE;
     }
     return VE_OK;
@@ -131,12 +159,13 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     ctx->noise_cb = nullptr; ctx->noise_user = nullptr; ctx->noise_host = nullptr;
     ve_default_params(&ctx->P);
     // Sweeps run one warp per node at every map size (measured: 1024^2 .. 8192^2; at 8192^2 the up-sweep
-    // takes 0.53 s per step against 1.1 s with eight one-thread nodes per warp).  VE_LANES_* > 1 selects
-    // the thread-per-node kernels instead (kept for comparison and covered by a test).
-    uint32_t auto_lanes = 1u;
-    ctx->lanes_down = getenv("VE_LANES_DOWN") ? (uint32_t)atoi(getenv("VE_LANES_DOWN")) : auto_lanes;
-    ctx->lanes_up = getenv("VE_LANES_UP") ? (uint32_t)atoi(getenv("VE_LANES_UP")) : auto_lanes;
-    ctx->lanes_other = getenv("VE_LANES_OTHER") ? (uint32_t)atoi(getenv("VE_LANES_OTHER")) : auto_lanes;
+    // takes 0.53 s per step against 1.1 s with eight one-thread nodes per warp).  ve_set_debug("lanes_*", k > 1)
+    // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
+    ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
+    ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
+    ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->spin_limit_ns = 0;
+    ctx->hist_count = 0;
+    ctx->up_ev_ready = false; ctx->up_ms_total = 0.0; ctx->up_launches_total = 0;
     *out = ctx;
     return create_impl(ctx, x_lg, y_lg, device_ids, n_devices);
 }
@@ -154,6 +183,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    if (ctx->up_ev_ready) for (int i = 0; i < 200; ++i) cudaEventDestroy(ctx->up_ev[i]);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->noise_host) cudaFreeHost(ctx->noise_host);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -161,6 +191,24 @@ void ve_destroy(ve_ctx* ctx) {
 }
 
 const char* ve_last_error(ve_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
+    if (!ctx || !key) return VE_ERR_INVALID;
+    std::string k(key);
+    if (k == "lanes_down") ctx->lanes_down = value < 1 ? 1u : (uint32_t)value;
+    else if (k == "lanes_up") ctx->lanes_up = value < 1 ? 1u : (uint32_t)value;
+    else if (k == "lanes_other") ctx->lanes_other = value < 1 ? 1u : (uint32_t)value;
+    else if (k == "df_bps") ctx->dbg_df_bps = (int)value;
+    else if (k == "newton") ctx->dbg_newton = (int)value;
+    else if (k == "newton_variant") ctx->dbg_newton_variant = (int)value;
+    else if (k == "lwv_small_log") ctx->dbg_lwv_small_log = (int)value;
+    else if (k == "thermal_sweep") ctx->dbg_thermal_sweep = (int)value;
+    else if (k == "lakes_trace") ctx->dbg_lakes_trace = (int)value;
+    else if (k == "serial_err") ctx->dbg_serial_err = (int)value;
+    else if (k == "spin_limit_ms") ctx->spin_limit_ns = (uint64_t)(value < 0 ? 0 : value) * 1000000ull;
+    else { ctx->err = "ve_set_debug: unknown key " + k; return VE_ERR_INVALID; }
+    return VE_OK;
+}
 
 int ve_set_params(ve_ctx* ctx, const ve_params* p) {
     if (!ctx || !p) return VE_ERR_INVALID;
@@ -228,10 +276,17 @@ int ve_set_state(ve_ctx* ctx, const double* h, const double* b, const double* wh
     return VE_OK;
 }
 
+// One NVTX range per stage of erode() (host-side range around the stage's launches; shows up in
+// nsys / ncu --nvtx), plus optional synchronising wall-clock timers (ve_set_timing).
 struct StageTimer {
-    ve_ctx* ctx; int id; std::chrono::steady_clock::time_point t0;
-    StageTimer(ve_ctx* c, int i) : ctx(c), id(i) { if (ctx->timing) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); } }
+    ve_ctx* ctx; int id; std::chrono::steady_clock::time_point t0; bool open;
+    ~StageTimer() { if (open) nvtxRangePop(); }                 // error return inside the stage
+    StageTimer(ve_ctx* c, int i) : ctx(c), id(i), open(true) {
+        nvtxRangePushA(TIMER_NAMES[i]);
+        if (ctx->timing) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); }
+    }
     void stop() {
+        nvtxRangePop(); open = false;
         if (ctx->timing) {
             cudaStreamSynchronize(ctx->stream);
             ctx->timers[id] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -242,7 +297,7 @@ struct StageTimer {
 // erode(): erosion.rs:699-1731
 int ve_step(ve_ctx* ctx) {
     if (!ctx) return VE_ERR_INVALID;
-    if (!ctx->nz.perm) { ctx->err = "ve_set_noise not called"; return VE_ERR_INVALID; }
+    if (!ctx->nz.perm && !ctx->noise_cb) { ctx->err = "no rock-strength source: call ve_set_noise or ve_set_noise_cb"; return VE_ERR_INVALID; }
     VE_CUDA(cudaSetDevice(ctx->device));
     const size_t nb8 = (size_t)ctx->g.n * 8;
     memset(ctx->timers, 0, sizeof(ctx->timers));
@@ -257,7 +312,8 @@ int ve_step(ve_ctx* ctx) {
     { StageTimer t(ctx, VT_AREA); VE_TRY(ve_g_area(ctx)); t.stop(); }                                                   // 841
     { StageTimer t(ctx, VT_SLOPE); VE_TRY(ve_k_max_slope(ctx)); t.stop(); }                                             // 845-856
     { StageTimer t(ctx, VT_KFACT); VE_TRY(ve_k_kfactors(ctx)); t.stop(); }                                              // 870-1006
-    VE_TRY(ve_g_spl_solve(ctx));                                                                                         // 1076-1475
+    nvtxRangePushA("gauss_seidel");
+    { int rc_gs = ve_g_spl_solve(ctx); nvtxRangePop(); VE_TRY(rc_gs); }                                                  // 1076-1475
     VE_TRY(ve_check_abort(ctx));
     { StageTimer t(ctx, VT_BASEMENT); VE_TRY(ve_k_basement(ctx)); t.stop(); }                                           // 1483-1556
     { StageTimer t(ctx, VT_THERMAL); VE_TRY(ve_g_thermal_wh(ctx)); VE_TRY(ve_k_thermal_kd(ctx));                        // 1597-1696
@@ -265,6 +321,8 @@ int ve_step(ve_ctx* ctx) {
     { StageTimer t(ctx, VT_DIFFUSION); VE_TRY(ve_k_diffusion(ctx, dt, ctx->h, ctx->b, ctx->kd_eff)); t.stop(); }        // 1717-1728
     VE_TRY(ve_check_abort(ctx));
     ctx->timers[VT_TOTAL] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_all).count();
+    ctx->hist_n_gs[ctx->hist_count & 255u] = ctx->n_gs; ctx->hist_n_lakes[ctx->hist_count & 255u] = ctx->n_lakes;
+    ctx->hist_count++;
     return VE_OK;
 }
 
@@ -359,11 +417,23 @@ double ve_get_scalar(ve_ctx* ctx, int which) {
         case VE_S_MAXH: return ctx->maxh;             case VE_S_BOUNDARY_LEN: return (double)ctx->boundary_len;
         case VE_S_N_LAKES: return (double)ctx->n_lakes; case VE_S_MAX_UPLIFT: return (double)ctx->max_uplift;
         case VE_S_MAX_G: return (double)ctx->max_g;   case VE_S_N_UNDERWATER: return (double)ctx->n_underwater;
+        case VE_S_UP_MS_TOTAL: return ctx->up_ms_total; case VE_S_UP_LAUNCHES_TOTAL: return (double)ctx->up_launches_total;
     }
     return NAN;
 }
 
 uint64_t ve_launch_count(ve_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int ve_get_history(ve_ctx* ctx, int32_t* n_gs, uint32_t* n_lakes, int cap) {
+    if (!ctx || cap < 0) return 0;
+    uint64_t have = ctx->hist_count < 256 ? ctx->hist_count : 256;
+    uint64_t k = have < (uint64_t)cap ? have : (uint64_t)cap;
+    for (uint64_t i = 0; i < k; ++i) {
+        uint64_t idx = (ctx->hist_count - k + i) & 255u;
+        if (n_gs) n_gs[i] = ctx->hist_n_gs[idx];
+        if (n_lakes) n_lakes[i] = ctx->hist_n_lakes[idx];
+    }
+    return (int)k;
+}
 int ve_set_timing(ve_ctx* ctx, int on) { if (!ctx) return VE_ERR_INVALID; ctx->timing = on != 0; return VE_OK; }
 int ve_get_timers(ve_ctx* ctx, double* dst, int cap) {
     int k = cap < VT_COUNT ? cap : (int)VT_COUNT;
@@ -425,16 +495,14 @@ int ve_get_multi_rec(ve_ctx* ctx, const double* h, const int32_t* dh, const uint
 
 int ve_get_multi_drainage(ve_ctx* ctx, const uint32_t* mstack, const uint8_t* mrec, const double* mwrec, double* area) {
     if (!ctx || !mstack || !mrec || !mwrec || !area) return VE_ERR_INVALID;
-    // The area sweep needs the sweep order and donor lists ve_g_stack derives; rebuilding them from
-    // a caller-supplied mstack would duplicate that stage, so this entry point requires that the
-    // context's last ve_get_multi_rec produced exactly these arrays (the only way the reference
-    // calls it: mod.rs:1480-1496 passes get_multi_rec's outputs straight through).
+    // A pure function of its arguments, as in the reference (erosion.rs:62-70): the three arrays are uploaded,
+    // the donor lists are rebuilt from them, and the area is gathered along mstack itself (donors first).
     VE_CUDA(cudaSetDevice(ctx->device));
     size_t n = ctx->g.n;
-    std::vector<uint32_t> chk(n);
-    VE_CUDA(cudaMemcpy(chk.data(), ctx->mstack, n * 4, cudaMemcpyDeviceToHost));
-    if (memcmp(chk.data(), mstack, n * 4) != 0) { ctx->err = "ve_get_multi_drainage: mstack is not the last ve_get_multi_rec result"; return VE_ERR_INVALID; }
-    VE_TRY(ve_g_area(ctx)); VE_TRY(ve_check_abort(ctx));
+    VE_CUDA(cudaMemcpyAsync(ctx->mstack, mstack, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->mrec, mrec, n, cudaMemcpyHostToDevice, ctx->stream));
+    VE_CUDA(cudaMemcpyAsync(ctx->mwrec, mwrec, n * 64, cudaMemcpyHostToDevice, ctx->stream));
+    VE_TRY(ve_g_area_from_stack(ctx)); VE_TRY(ve_check_abort(ctx));
     VE_CUDA(cudaMemcpyAsync(area, ctx->area, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
     VE_CUDA(cudaStreamSynchronize(ctx->stream));
     return VE_OK;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <map>
 #include <string>
 #include <vector>
 #include "../../include/velerode.h"
@@ -68,6 +69,16 @@ struct ve_ctx {
     uint32_t *order_td;       // topological order, sources first (wh desc, stack position asc)
     uint32_t *level;          // longest path to a sink, per node
     uint32_t lanes_down, lanes_up, lanes_other;   // active lanes per warp in the sweeps
+    // test / tuning knobs (ve_set_debug); all zero by default
+    int dbg_df_bps;           // resident blocks per SM for the sweeps (0: occupancy)
+    int dbg_newton;           // bit 0: skip the Newton loop, bit 2: force the slow re-solve of every node
+    int dbg_lwv_small_log;    // replay the lake_water_volume log before every Gauss-Seidel iteration
+    int dbg_thermal_sweep;    // ordered sweep instead of pointer jumping for the thermal water level
+    int dbg_lakes_trace;      // print per-phase times of get_lakes to stderr
+    int dbg_newton_variant;   // Newton loop variant of the up-sweep (0: default)
+    int dbg_serial_err;       // 1: always recompute the Gauss-Seidel error in the reference's serial order
+    uint64_t spin_limit_ns;   // give-up time of a polling worker (0: default scaled with the map size)
+    std::map<const void*, std::pair<int, size_t>> occ_cache;   // kernel -> (resident blocks per SM, dynamic smem)
     uint32_t *order_bu;       // nodes sorted by level (longest path to a sink): sinks first
     uint32_t *don_order;      // packed donor slots sorted by stack position
     uint32_t *don_live;       // the same without egress donors (dh < 0), for the sediment sweep
@@ -83,6 +94,13 @@ struct ve_ctx {
     void* cub_tmp; size_t cub_tmp_bytes;
     double* d_scalars;        // small device scalar block
     double* h_scalars;        // pinned mirror
+    // CUDA events around every up-sweep launch (the dominant kernel), read back at the end of the solve: live
+    // per-launch device time without extra synchronisation (bench.py's roofline line)
+    cudaEvent_t up_ev[200];
+    bool up_ev_ready;
+    double up_ms_total; uint64_t up_launches_total;
+    // per-step history since ve_create (ring of the last 256 steps): Gauss-Seidel iterations and lake counts
+    int hist_n_gs[256]; uint32_t hist_n_lakes[256]; uint64_t hist_count;
     // last-step scalars
     int n_gs; double gs_err; double maxh; uint64_t boundary_len; uint32_t n_lakes; uint32_t n_underwater;
 };
@@ -112,6 +130,10 @@ struct ve_ctx {
 
 static inline unsigned ve_blocks(uint64_t n, unsigned bs) { return (unsigned)((n + bs - 1) / bs); }
 
+// resident blocks per SM of `func` at this block size / dynamic shared memory, cached per context; the
+// >48 KB shared-memory opt-in is made per device
+int ve_occupancy(ve_ctx* ctx, const void* func, int block, size_t smem, int* bps_out);
+uint64_t ve_spin_limit_ns(const ve_ctx* ctx);
 // scratch buffer i with at least `bytes` bytes (grown on demand; contents undefined)
 int ve_scratch(ve_ctx* ctx, int i, size_t bytes, void** out);
 int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out);
@@ -131,6 +153,7 @@ int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* k
 int ve_g_wh_fill(ve_ctx* ctx);              // erosion.rs:2383-2400 along newh
 int ve_g_stack(ve_ctx* ctx);                // exact mstack + stackpos + order_td + don_order
 int ve_g_area(ve_ctx* ctx);
+int ve_g_area_from_stack(ve_ctx* ctx);      // area from ctx->mstack/mrec/mwrec alone (standalone get_multi_drainage)
 int ve_g_spl_solve(ve_ctx* ctx);            // Gauss-Seidel loop (erosion.rs:1076-1467)
 int ve_g_thermal_wh(ve_ctx* ctx);           // wh running max along newh (erosion.rs:1620, 1685)
 int ve_g_get_drainage(ve_ctx* ctx, const uint32_t* newh, const int32_t* dh, float* flux);

@@ -573,7 +573,7 @@ __global__ void __launch_bounds__(256) k_indirection(uint32_t n, const int32_t* 
 
 struct PhaseClock {
     bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0; const char* last;
-    PhaseClock(cudaStream_t s) : on(getenv("VE_DEBUG_LAKES") != nullptr), st(s), last(nullptr) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+    PhaseClock(cudaStream_t s, bool enable) : on(enable), st(s), last(nullptr) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
     void mark(const char* name) {
         if (!on) return;
         cudaStreamSynchronize(st);
@@ -585,7 +585,7 @@ struct PhaseClock {
 
 int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh) {
     const Geom& g = ctx->g;
-    PhaseClock pc(ctx->stream);
+    PhaseClock pc(ctx->stream, ctx->dbg_lakes_trace != 0);
     const uint32_t n = g.n;
     const unsigned nb = ve_blocks(n, 256);
     cudaStream_t st = ctx->stream;
@@ -723,11 +723,8 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_TRY(ve_scratch(ctx, 4, std::max((size_t)n * 8, lk), (void**)&connected)); // bfskey no longer needed
         VE_CUDA(cudaMemsetAsync(connected, 0, lk, st));
         {
-            static bool attr_set = false;
-            if (!attr_set) {
-                VE_CUDA(cudaFuncSetAttribute(k_lake_connect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(HEAP_SMEM_MAX * 32)));
-                attr_set = true;
-            }
+            int occ_unused = 0;   // per device: opts k_lake_connect in to 200 KB of dynamic shared memory
+            VE_TRY(ve_occupancy(ctx, (const void*)k_lake_connect, 32, (size_t)HEAP_SMEM_MAX * 32, &occ_unused));
             // shared memory: connected bitmap first (if it fits), the top of the heap in what is left
             uint32_t conn_words = (uint32_t)((lk + 31) / 32);
             if ((size_t)conn_words * 4 > 96 * 1024) conn_words = 0;

@@ -22,11 +22,12 @@ _DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirecti
                kfs=np.float32, kdf=np.float32, h_spl=np.float64, lake_silt=np.float64, lake_sill=np.int32,
                lake_water_volume=np.float64, kd_eff=np.float64, dh0=np.int32, wh_mrec=np.float64, b_spl=np.float64,
                h_pre_diff=np.float64)
-SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater"]
+SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater", "up_ms_total",
+           "up_launches_total"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
-           "ve_set_noise_cb", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
-           "ve_get_scalar", "ve_launch_count", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
+           "ve_set_noise_cb", "ve_set_debug", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
+           "ve_get_scalar", "ve_launch_count", "ve_get_history", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
            "ve_map_edge_factor", "ve_horizon_map"]
@@ -127,6 +128,11 @@ class ErosionContext:
             setattr(prm, k, float(v))
         self._chk(lib().ve_set_params(self.ctx, ctypes.byref(prm)))
 
+    def set_debug(self, **kw):
+        """Test / tuning knobs of ve_set_debug (lanes_up=8, newton=4, spin_limit_ms=200, ...)."""
+        for k, v in kw.items():
+            self._chk(lib().ve_set_debug(self.ctx, k.encode(), ctypes.c_longlong(int(v))))
+
     def set_noise(self, noise):
         perm = np.ascontiguousarray(noise["perm"], np.uint8)
         nz = Noise(int(noise["octaves"]), float(noise["frequency"]), float(noise["lacunarity"]),
@@ -208,6 +214,13 @@ class ErosionContext:
 
     def launch_count(self):
         return int(lib().ve_launch_count(self.ctx))
+
+    def history(self, last):
+        """(n_gs, n_lakes) lists of the last `last` erode() steps."""
+        g = (ctypes.c_int32 * last)()
+        l = (ctypes.c_uint32 * last)()
+        k = lib().ve_get_history(self.ctx, g, l, int(last))
+        return list(g[:k]), list(l[:k])
 
     def set_timing(self, on=True):
         self._chk(lib().ve_set_timing(self.ctx, int(on)))
