@@ -8,9 +8,11 @@ A "step" is one erode() (world/src/sim/erosion.rs:699) over the whole map.  Work
 BASELINE.json configs[1]: the default 1024x1024 world (MapSizeLg 10x10) with the synthetic fields
 of veloren_b200.synth (reference recipes, in-repo noise).  `value` = N_cells * K / device time,
 state resident in HBM; `e2e` = the same through the public call with host buffers (inputs H2D,
-results D2H inside the timed region).  With --gpus N>1 each rank erodes its own world (the
-reference scales the same way: world/examples/batch_generate.rs runs k independent generations);
-no data-path collective, weak scaling, value = sum over ranks / max time.
+results D2H inside the timed region).  With --gpus N>1 every rank erodes its own copy of the SAME
+world (replicas: the reference scales the same way, world/examples/batch_generate.rs runs k
+independent generations); no data-path collective, weak scaling, value = sum over ranks / max time.
+The reference arm at N>1 runs N oracle instances concurrently on the host cores (cores/N OpenMP
+threads each), i.e. the same N-world job.
 """
 import argparse
 import json
@@ -29,8 +31,17 @@ X_LG = Y_LG = 10
 # algorithmic bytes per cell of the dominant kernel (G4, the implicit up-sweep)
 G4_BYTES_PER_CELL = 145
 FIXED_BYTES_PER_CELL, GS_BYTES_PER_CELL = 684, 374
-# dram__bytes_read.sum + dram__bytes_write.sum of one up-sweep launch (ncu --set full, round 1)
-NCU_TRAFFIC_BYTES = 146022144 + 30922240
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per up-sweep launch from the committed ncu --set full capture
+    (profiles/r02_ncu_traffic.json); None when no capture of the current kernel exists."""
+    p = os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")
+    try:
+        d = json.load(open(p))
+        return d["OpGsUp"]["dram_bytes_per_launch"], d["OpGsUp"].get("source", p)
+    except Exception:
+        return None, None
 
 
 def peaks():
@@ -81,30 +92,44 @@ def dist_env():
 
 def run_reference(args):
     """CPU arm: the oracle (restatement of the reference; the reference itself is Rust and cannot be
-    built in this image) on all host cores, same config/metric.  Rank 0 only."""
+    built in this image) on all host cores, same config/metric.  Rank 0 only.  At N>1 the job is N
+    copies of the world, so N oracle instances run concurrently, cores/N OpenMP threads each."""
     rank, world, _ = dist_env()
     if rank != 0:
         return
     from veloren_b200 import synth
     from oracle import pyoracle as po
-    fields = synth.generate(X_LG, Y_LG)
-    o = po.Oracle(fields, n_threads=os.cpu_count())   # torchrun exports OMP_NUM_THREADS=1: ask for all cores explicitly
-    n = o.n
-    for _ in range(args.warmup):
-        o.step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        o.step()
-    dt = time.perf_counter() - t0
+    nw = max(1, args.gpus)
     cores = os.cpu_count()
-    v = n * args.steps / dt / 1e6
+    per = max(1, cores // nw)
+    fields = synth.generate(X_LG, Y_LG)
+    oracles = [po.Oracle(fields, n_threads=per) for _ in range(nw)]   # torchrun exports OMP_NUM_THREADS=1: ask explicitly
+    n = oracles[0].n
+
+    def steps(k):
+        if nw == 1:
+            for _ in range(k):
+                oracles[0].step()
+            return
+        ths = [threading.Thread(target=lambda o=o: [o.step() for _ in range(k)]) for o in oracles]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+
+    steps(args.warmup)
+    t0 = time.perf_counter()
+    steps(args.steps)
+    dt = time.perf_counter() - t0
+    v = n * nw * args.steps / dt / 1e6
     line = {"impl": "reference", "metric": "erosion_mcell_iters_per_s", "value": v, "unit": "Mcell-iters/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(1),
+            "config": workload_config(nw),
             "cpu_baseline": {"value": v, "unit": "Mcell-iters/s", "cores": cores, "kind": "port",
-                             "sample": "%d erode() steps of the 1024x1024 world after %d warm-up steps, C++ oracle "
-                                       "(OpenMP where the reference uses rayon)" % (args.steps, args.warmup)},
+                             "sample": "%d erode() steps of %d copy(ies) of the 1024x1024 world after %d warm-up steps, C++ oracle "
+                                       "(OpenMP where the reference uses rayon; %d threads per world); parity with the Rust "
+                                       "reference unpinned" % (args.steps, nw, args.warmup, per)},
             "e2e": {"value": v, "unit": "Mcell-iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -112,7 +137,7 @@ def run_reference(args):
 def workload_config(n_gpus):
     return {"workload": "default 1024x1024 world (MapSizeLg 10x10), erode() steps of the WorldSim::generate schedule",
             "x_lg": X_LG, "y_lg": Y_LG, "seed": 130626853, "scale": 2.0,
-            "parallelism": "1 world per GPU (%d independent worlds)" % n_gpus,
+            "parallelism": "replicas: %d independent copies of the same world, one per GPU, no data-path collective" % n_gpus,
             "l2": "working set ~0.7 GB per world > 126 MB L2 (no flush needed)"}
 
 
@@ -127,7 +152,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    # every rank erodes its own world (different seed per rank), inputs resident before timing
+    # every rank erodes its own copy of the same world (same seed: efficiency then measures the machine,
+    # not the world), inputs resident before timing
     from veloren_b200 import multi
     fields = synth.generate(X_LG, Y_LG, seed=multi.seed_for_rank(rank))
     n = (1 << X_LG) * (1 << Y_LG)
@@ -146,29 +172,30 @@ def run_ours(args):
         sampler.start()
     barrier()
     l0 = ctx.launch_count()
-    ms = ctx.run_device_timed(args.steps)
+    up_ms0, up_n0 = ctx.scalar("up_ms_total"), ctx.scalar("up_launches_total")
+    ms = ctx.run_device_timed(args.steps)        # CUDA events on the library's stream around exactly K steps
+    gs_counts, lake_counts = ctx.history(args.steps)
     launches = ctx.launch_count() - l0
+    up_ms = ctx.scalar("up_ms_total") - up_ms0
+    up_n = int(ctx.scalar("up_launches_total") - up_n0)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     value, ms_max = multi.aggregate_mcell_iters_per_s(n, args.steps, ms, device="cuda")
+    per_rank = multi.gather_objects({"rank": rank, "ms_per_step": ms / args.steps, "n_gs": gs_counts, "n_lakes": lake_counts})
 
-    # ---- roofline of the dominant kernel (G4 up-sweep), timed live with CUDA events ----------
-    ctx.set_timing(True)
-    up_s, n_gs_tot, gs_counts = 0.0, 0, []
-    for _ in range(2):
-        ctx.step()
-        tm = ctx.timers()
-        up_s += tm["gs_up"]
-        n_gs_tot += int(ctx.scalar("n_gs"))
-        gs_counts.append(int(ctx.scalar("n_gs")))
-    ctx.set_timing(False)
+    # ---- roofline of the dominant kernel (G4 up-sweep): CUDA events recorded around every launch of the
+    # timed steps themselves, on the stream it is launched on ----------------------------------------
     peak, how = peaks()
-    per_launch = up_s / max(n_gs_tot, 1)
+    per_launch = up_ms * 1e-3 / max(up_n, 1)
     achieved = G4_BYTES_PER_CELL * n / per_launch / 1e9
+    traffic, traffic_src = ncu_traffic()
     roofline = {"bound": "hbm", "kernel": "k_sweep_warp<OpGsUp> (implicit stream-power up-sweep, erosion.rs:1237-1450)",
                 "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r01g_ncu_full_OpGsUp.txt (dram read 146.02 MB + write 30.92 MB per launch)", "avg_launch_ms": per_launch * 1e3, "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
-                "n_gs_per_step": gs_counts}
+                "traffic": traffic, "traffic_source": traffic_src, "avg_launch_ms": per_launch * 1e3,
+                "launches_timed": up_n, "share_of_step": up_ms / ms if ms > 0 else None,
+                "algorithmic_bytes_per_launch": G4_BYTES_PER_CELL * n,
+                "whole_step_bytes": (FIXED_BYTES_PER_CELL + GS_BYTES_PER_CELL * (sum(gs_counts) / max(len(gs_counts), 1))) * n,
+                "note": "latency-bound by the dependency depth of the receiver DAG at 1024^2 (DESIGN.md section 7)"}
 
     # ---- e2e: public call with host buffers (pinned), H2D inputs + K steps + D2H results -----
     pinned = {}
@@ -191,6 +218,26 @@ def run_ours(args):
            "note": "ErosionContext.set_inputs + run(K) from the initial state: inputs H2D once per call, (h,b) D2H at the end",
            "checksum_h": float(out_h.sum())}
 
+    # ---- the metric's second half: full do_erosion wall time (100 steps + the zero-step f32 round trip of the
+    # second call, mod.rs:1370-1421) through the public host API, copies and context creation included ----------
+    full = None
+    if not args.no_full:
+        barrier()
+        t0 = time.perf_counter()
+        c2 = ErosionContext(X_LG, Y_LG, device=local)
+        c2.configure(pinned | {k: fields[k] for k in ("k_d_scale", "k_da", "noise")})
+        hf, bf = c2.run(100)
+        f2 = dict(pinned); f2["oldh"], f2["oldb"] = hf.astype(np.float32), bf.astype(np.float32)
+        c2.set_inputs(f2)
+        h2, _ = c2.run(0)
+        torch.cuda.synchronize()
+        tfull = time.perf_counter() - t0
+        c2.close()
+        tfull_max = multi.max_over_ranks(tfull, device="cuda")
+        full = {"wall_s": tfull_max, "steps": 100, "mcell_iters_per_s": n * 100 * world / tfull_max / 1e6,
+                "f32_round_trip_ok": bool(np.array_equal(h2, hf.astype(np.float32).astype(np.float64))),
+                "checksum_h": float(hf.sum())}
+
     # ---- CPU baseline on the box's host cores (rank 0, N=1 only): bounded sample ---------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -211,7 +258,8 @@ def run_ours(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-                "gpu_launches": int(launches), "clocks": clocks,
+                "gpu_launches": int(launches), "clocks": clocks, "per_rank": per_rank,
+                "full_do_erosion": full,
                 "full_do_erosion_estimate_s": ms_max / args.steps * 100 / 1e3}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -225,6 +273,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-full", action="store_true", help="skip the measured 100-step do_erosion run")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

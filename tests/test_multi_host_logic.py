@@ -1,4 +1,4 @@
-"""world_size-2 gloo test of the multi-GPU host logic (replicas: per-rank seeds, max-over-ranks
+"""world_size-2 gloo test of the multi-GPU host logic (replicas of one world, max-over-ranks
 timing, whole-job throughput), on CPU."""
 import os
 import socket
@@ -23,7 +23,8 @@ def _worker(rank, world, port, q):
     f = synth.generate(4, 4, seed=seed)
     local_ms = 10.0 + 5.0 * rank                     # rank 1 is the slow one
     v, ms = multi.aggregate_mcell_iters_per_s(256, 2, local_ms)
-    q.put((rank, seed, float(f["oldh"].sum()), v, ms))
+    objs = multi.gather_objects({"rank": rank, "ms": local_ms})
+    q.put((rank, seed, float(f["oldh"].sum()), v, ms, [o["ms"] for o in objs]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -39,8 +40,9 @@ def test_two_ranks_replicas():
     for p in ps:
         p.join(timeout=60)
         assert p.exitcode == 0
-    (r0, s0, sum0, v0, ms0), (r1, s1, sum1, v1, ms1) = res
-    assert s1 == s0 + 1 and sum0 != sum1              # different worlds per rank
+    (r0, s0, sum0, v0, ms0, g0), (r1, s1, sum1, v1, ms1, g1) = res
+    assert s1 == s0 and sum0 == sum1                  # replicas of the same world on every rank
+    assert g0 == g1 == [10.0, 15.0]                   # per-rank times reach every rank
     assert ms0 == ms1 == 15.0                         # max over ranks
     assert v0 == v1 == 256 * 2 * 2 / 15e-3 / 1e6      # whole-job aggregate
 

@@ -12,8 +12,18 @@ BASE_SEED = 130626853  # DEFAULT_WORLD_SEED, world/src/sim/mod.rs:586
 
 
 def seed_for_rank(rank):
-    """Every rank erodes its own world: rank r gets seed BASE_SEED + r."""
-    return BASE_SEED + int(rank)
+    """Every rank erodes its own copy of the SAME world (BASE_SEED): with a seed per rank the step time
+    varied 2x from world to world and the scaling figure measured the worlds, not the machine."""
+    return BASE_SEED
+
+
+def gather_objects(obj):
+    """list of every rank's object on every rank (identity list when not initialised)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [obj]
+    out = [None] * dist.get_world_size()
+    dist.all_gather_object(out, obj)
+    return out
 
 
 def max_over_ranks(value, device="cpu"):
