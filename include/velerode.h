@@ -83,7 +83,8 @@ typedef enum {
     VE_S_N_GS = 0, VE_S_ERR, VE_S_MAXH, VE_S_BOUNDARY_LEN, VE_S_N_LAKES, VE_S_MAX_UPLIFT, VE_S_MAX_G,
     VE_S_N_UNDERWATER,
     VE_S_UP_MS_TOTAL,        /* device milliseconds spent in up-sweep launches since ve_create (CUDA events) */
-    VE_S_UP_LAUNCHES_TOTAL   /* number of up-sweep launches since ve_create */
+    VE_S_UP_LAUNCHES_TOTAL,  /* number of up-sweep launches since ve_create */
+    VE_S_LAKE_ROUNDS         /* fixed-point rounds of the last parallel lake growth (0: the serial path ran) */
 } ve_scalar;
 
 void ve_default_params(ve_params* p);
@@ -98,7 +99,8 @@ const char* ve_last_error(ve_ctx* ctx);
 /* Test and tuning knobs (no counterpart in the reference; defaults are what production uses).  Keys:
  * "lanes_up" / "lanes_down" / "lanes_other" (k > 1: thread-per-node sweeps), "df_bps" (resident blocks per SM
  * of the sweeps), "newton" (bit 0: skip the Newton loop, bit 2: force the slow re-solve), "newton_variant",
- * "lwv_small_log", "thermal_sweep", "lakes_trace", "serial_err" (always sum the Gauss-Seidel error in the
+ * "lwv_small_log", "thermal_sweep", "lakes_trace", "lakes_serial" (one-warp heap growth of the lake forest),
+ * "poll_sleep_ns", "serial_err" (always sum the Gauss-Seidel error in the
  * reference's serial order), "spin_limit_ms" (give-up time of a stalled sweep). */
 int ve_set_debug(ve_ctx* ctx, const char* key, long long value);
 int ve_set_params(ve_ctx* ctx, const ve_params* p);

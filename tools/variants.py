@@ -20,6 +20,6 @@ for spec in sys.argv[4:]:
         c.step()
         for k, v in c.timers().items():
             acc[k] = acc.get(k, 0.0) + v * 1e3 / 3
-    print(json.dumps({"variant": name, "knobs": knobs, "ms_per_step": ms / steps, "n_gs_last": int(c.scalar("n_gs")),
+    print(json.dumps({"variant": name, "knobs": knobs, "ms_per_step": ms / steps, "n_gs_last": int(c.scalar("n_gs")), "lake_rounds": int(c.scalar("lake_rounds")),
                       "stage_ms_next3": {k: round(v, 2) for k, v in acc.items()}}), flush=True)
     c.close()

@@ -163,7 +163,8 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->spin_limit_ns = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0;
+    ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
     ctx->hist_count = 0;
     ctx->up_ev_ready = false; ctx->up_ms_total = 0.0; ctx->up_launches_total = 0;
     *out = ctx;
@@ -182,7 +183,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->don_order, ctx->don_live, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
-    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     if (ctx->up_ev_ready) for (int i = 0; i < 200; ++i) cudaEventDestroy(ctx->up_ev[i]);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->noise_host) cudaFreeHost(ctx->noise_host);
@@ -204,7 +205,9 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "lwv_small_log") ctx->dbg_lwv_small_log = (int)value;
     else if (k == "thermal_sweep") ctx->dbg_thermal_sweep = (int)value;
     else if (k == "lakes_trace") ctx->dbg_lakes_trace = (int)value;
+    else if (k == "lakes_serial") ctx->dbg_lakes_serial = (int)value;
     else if (k == "serial_err") ctx->dbg_serial_err = (int)value;
+    else if (k == "poll_sleep_ns") ctx->dbg_poll_sleep_ns = (int)value;
     else if (k == "spin_limit_ms") ctx->spin_limit_ns = (uint64_t)(value < 0 ? 0 : value) * 1000000ull;
     else { ctx->err = "ve_set_debug: unknown key " + k; return VE_ERR_INVALID; }
     return VE_OK;
@@ -417,6 +420,7 @@ double ve_get_scalar(ve_ctx* ctx, int which) {
         case VE_S_MAXH: return ctx->maxh;             case VE_S_BOUNDARY_LEN: return (double)ctx->boundary_len;
         case VE_S_N_LAKES: return (double)ctx->n_lakes; case VE_S_MAX_UPLIFT: return (double)ctx->max_uplift;
         case VE_S_MAX_G: return (double)ctx->max_g;   case VE_S_N_UNDERWATER: return (double)ctx->n_underwater;
+        case VE_S_LAKE_ROUNDS: return (double)ctx->lake_rounds;
         case VE_S_UP_MS_TOTAL: return ctx->up_ms_total; case VE_S_UP_LAUNCHES_TOTAL: return (double)ctx->up_launches_total;
     }
     return NAN;

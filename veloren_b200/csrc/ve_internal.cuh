@@ -75,7 +75,10 @@ struct ve_ctx {
     int dbg_lwv_small_log;    // replay the lake_water_volume log before every Gauss-Seidel iteration
     int dbg_thermal_sweep;    // ordered sweep instead of pointer jumping for the thermal water level
     int dbg_lakes_trace;      // print per-phase times of get_lakes to stderr
+    int dbg_lakes_serial;     // 1: grow the lake forest with the one-warp heap (round 1) instead of the parallel formulation
+    uint32_t lake_rounds;     // fixed-point rounds of the last parallel lake growth (0: serial path was used)
     int dbg_newton_variant;   // Newton loop variant of the up-sweep (0: default)
+    int dbg_poll_sleep_ns;    // pause between poll rounds of the warp-per-node sweeps (0: none)
     int dbg_serial_err;       // 1: always recompute the Gauss-Seidel error in the reference's serial order
     uint64_t spin_limit_ns;   // give-up time of a polling worker (0: default scaled with the map size)
     std::map<const void*, std::pair<int, size_t>> occ_cache;   // kernel -> (resident blocks per SM, dynamic smem)
@@ -89,8 +92,8 @@ struct ve_ctx {
     // forest scratch (mstack / lakes)
     uint32_t *f_parent, *f_jump, *f_depth, *f_root;
     // generic scratch
-    void* scratch[8];
-    size_t scratch_bytes[8];
+    void* scratch[12];
+    size_t scratch_bytes[12];
     void* cub_tmp; size_t cub_tmp_bytes;
     double* d_scalars;        // small device scalar block
     double* h_scalars;        // pinned mirror

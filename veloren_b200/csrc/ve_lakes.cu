@@ -15,6 +15,7 @@
 #include "ve_internal.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cooperative_groups.h>
 #include <algorithm>
 #include <string.h>
 #include <stdlib.h>
@@ -403,6 +404,386 @@ __global__ void __launch_bounds__(32) k_lake_connect(const uint32_t* __restrict_
                      n_flows_out[3] = (uint32_t)(t_sift >> 10); n_flows_out[4] = (uint32_t)(t_scan >> 10); n_flows_out[5] = (uint32_t)(t_push >> 10); }
 }
 
+// ---- (iii)/(iv) parallel formulation ----------------------------------------------------------------
+// The reference grows the forest Prim-style from the boundary lakes with a heap keyed
+// (pass height, cell on the side being connected, cell on the connected side) (erosion.rs:2060-2137).
+// Two facts turn that into parallel work (checked against the oracle's heap loop on every test map):
+//  1. If every pass had ONE fixed key, the growth would be Prim's algorithm on a graph with distinct
+//     weights: the passes it uses are the minimum spanning tree (all boundary lakes = one vertex S), each
+//     lake's pass is its parent edge in the tree rooted at S, and the ORDER of connection is the pre-order
+//     of the tree T' in which parent'(v) = the lower end of the nearest ancestor edge heavier than v's own
+//     parent edge (S if none), children visited by ascending key: after a heavy edge is taken, everything
+//     reachable below it by lighter edges is connected before anything else.
+//  2. The key of a pass depends on the direction in which it is crossed, i.e. on which of its two lakes is
+//     connected first.  Given a guess of the connection order, orient every pass by it, run 1, and obtain a
+//     new order; the reference's order is the unique fixed point of that map (a run of Prim with the keys
+//     of a fixed point only ever compares candidates whose key is the one the reference would compute, so
+//     it is the reference's run).  Only passes that share their height with another pass can change rank,
+//     so the iteration has converged as soon as their orientation repeats: 2-3 rounds in practice.
+// Per round: orientation + rank inside the (tiny) equal-height groups, Boruvka rounds in one cooperative
+// kernel, rooting by Euler tour + list ranking, nearest-heavier-ancestor by binary lifting, one radix
+// sort, a second Euler tour.  No round is sequential in the number of lakes.
+namespace cg = cooperative_groups;
+#define LG_NONE 0xffffffffu
+#define LG_MAX_GROUP 2048u     /* equal-height groups are ranked by brute force; larger ones take the serial path */
+
+__global__ void __launch_bounds__(256) k_lg_edges(uint32_t cap, PassTable t, const int32_t* __restrict__ dh0, const uint32_t* __restrict__ lrank,
+                                                  uint32_t L, uint32_t* __restrict__ counter, uint64_t* __restrict__ ehb,
+                                                  uint32_t* __restrict__ idx, uint4* __restrict__ erec) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= cap || t.key[s] == 0) return;
+    uint64_t pk = t.key[s] - 1ull;
+    uint32_t A = (uint32_t)(pk >> 32), B = (uint32_t)pk;
+    uint64_t e = t.edge[s];
+    uint32_t i = atomicAdd(counter, 1u);
+    ehb[i] = t.hb[s];
+    idx[i] = i;
+    erec[i] = make_uint4(dh0[A] == -1 ? lrank[A] : L, dh0[B] == -1 ? lrank[B] : L, (uint32_t)(e >> 32), (uint32_t)e);
+}
+__global__ void __launch_bounds__(256) k_lg_gather(uint32_t M, const uint32_t* __restrict__ idx, const uint4* __restrict__ in, uint4* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < M) out[i] = in[idx[i]];
+}
+// equal-height groups in the height-sorted edge array: [gs, ge) for every position
+__global__ void __launch_bounds__(256) k_lg_groups(uint32_t M, const uint64_t* __restrict__ hb, uint32_t* __restrict__ gs, uint32_t* __restrict__ ge,
+                                                   int* __restrict__ toolarge) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    const uint64_t h = hb[i];
+    uint32_t a = i, b = i + 1;
+    while (a > 0 && hb[a - 1] == h && i - a < LG_MAX_GROUP) --a;
+    while (b < M && hb[b] == h && b - i < LG_MAX_GROUP) ++b;
+    if (i - a >= LG_MAX_GROUP || b - i >= LG_MAX_GROUP) *toolarge = 1;
+    gs[i] = a; ge[i] = b;
+}
+// orientation of every pass by the current guess of the connection order; key_lo = (from cell, to cell) as the heap
+// would see it; `changed` is raised when a pass that shares its height changes orientation
+__global__ void __launch_bounds__(256) k_lg_orient(uint32_t M, const uint4* __restrict__ erec, const uint32_t* __restrict__ pos,
+                                                   const uint32_t* __restrict__ gs, const uint32_t* __restrict__ ge, uint8_t* __restrict__ obits,
+                                                   uint64_t* __restrict__ key_lo, int first, int* __restrict__ changed) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    uint4 x = erec[i];
+    const bool a_later = pos[x.x] > pos[x.y];
+    const uint32_t from = a_later ? x.z : x.w, to = a_later ? x.w : x.z;
+    key_lo[i] = ((uint64_t)from << 32) | (uint64_t)to;
+    const uint8_t bit = a_later ? 1 : 0;
+    if (!first && ge[i] - gs[i] > 1u && obits[i] != bit) *changed = 1;
+    obits[i] = bit;
+}
+__global__ void __launch_bounds__(256) k_lg_rank(uint32_t M, const uint32_t* __restrict__ gs, const uint32_t* __restrict__ ge,
+                                                 const uint64_t* __restrict__ key_lo, uint32_t* __restrict__ erank, uint32_t* __restrict__ byrank) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    const uint32_t a = gs[i], b = ge[i];
+    uint32_t r = a;
+    const uint64_t k = key_lo[i];
+    for (uint32_t j = a; j < b; ++j) r += key_lo[j] < k ? 1u : 0u;
+    erank[i] = r;
+    byrank[r] = i;
+}
+// Boruvka: every component takes its lightest outgoing pass (ranks are distinct, so the hooks form a forest plus
+// 2-cycles, which are broken towards the smaller id); rounds until no pass joins two components.
+__global__ void __launch_bounds__(256) k_lg_boruvka(uint32_t M, uint32_t V, const uint4* __restrict__ erec, const uint32_t* __restrict__ erank,
+                                                    const uint32_t* __restrict__ byrank, uint32_t* comp_a, uint32_t* comp_b, uint32_t* best,
+                                                    volatile uint32_t* hook, uint8_t* intree, volatile uint32_t* flags, uint32_t* out_sel) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (uint32_t v = tid; v < V; v += nth) comp_a[v] = v;
+    for (uint32_t e = tid; e < M; e += nth) intree[e] = 0;
+    uint32_t* comp = comp_a; uint32_t* comp2 = comp_b;
+    grid.sync();
+    for (int round = 0; round < 64; ++round) {
+        for (uint32_t v = tid; v < V; v += nth) best[v] = LG_NONE;
+        grid.sync();
+        bool any = false;
+        for (uint32_t e = tid; e < M; e += nth) {
+            uint4 x = erec[e];
+            uint32_t ca = comp[x.x], cb = comp[x.y];
+            if (ca != cb) { uint32_t r = erank[e]; atomicMin(best + ca, r); atomicMin(best + cb, r); any = true; }
+        }
+        if (any) flags[round] = 1u;
+        grid.sync();
+        if (flags[round] == 0u) break;
+        for (uint32_t v = tid; v < V; v += nth) {
+            uint32_t h = v;
+            if (comp[v] == v) {
+                uint32_t b = best[v];
+                if (b != LG_NONE) {
+                    uint32_t e = byrank[b];
+                    uint4 x = erec[e];
+                    uint32_t ca = comp[x.x];
+                    h = (ca == v) ? comp[x.y] : ca;
+                    intree[e] = 1;
+                }
+            }
+            hook[v] = h;
+        }
+        grid.sync();
+        for (uint32_t v = tid; v < V; v += nth) {
+            uint32_t w = hook[v];
+            if (w != v && hook[w] == v && v < w) hook[v] = v;
+        }
+        grid.sync();
+        for (uint32_t v = tid; v < V; v += nth) {
+            uint32_t r = comp[v];
+            for (;;) { uint32_t h = hook[r]; if (h == r) break; r = h; }
+            comp2[v] = r;
+        }
+        grid.sync();
+        uint32_t* tsw = comp; comp = comp2; comp2 = tsw;
+    }
+    if (tid == 0) *out_sel = (comp == comp_a) ? 0u : 1u;
+}
+__global__ void __launch_bounds__(256) k_lg_check(uint32_t V, const uint32_t* __restrict__ comp, int* __restrict__ bad) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < V && comp[v] != comp[V - 1]) *bad = 1;          // some lake cannot reach the boundary
+}
+__global__ void __launch_bounds__(256) k_lg_deg(uint32_t M, const uint4* __restrict__ erec, const uint8_t* __restrict__ intree, uint32_t* __restrict__ deg) {
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= M || !intree[e]) return;
+    uint4 x = erec[e];
+    atomicAdd(deg + x.x, 1u); atomicAdd(deg + x.y, 1u);
+}
+__global__ void __launch_bounds__(256) k_lg_arcs(uint32_t M, const uint4* __restrict__ erec, const uint8_t* __restrict__ intree, const uint32_t* __restrict__ off,
+                                                 uint32_t* __restrict__ cur, uint32_t* __restrict__ arc_to, uint32_t* __restrict__ arc_twin,
+                                                 uint32_t* __restrict__ arc_e) {
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= M || !intree[e]) return;
+    uint4 x = erec[e];
+    uint32_t sa = off[x.x] + atomicAdd(cur + x.x, 1u), sb = off[x.y] + atomicAdd(cur + x.y, 1u);
+    arc_to[sa] = x.y; arc_twin[sa] = sb; arc_e[sa] = e;
+    arc_to[sb] = x.x; arc_twin[sb] = sa; arc_e[sb] = e;
+}
+// Euler circuit of the doubled tree, cut open at S's first arc
+__global__ void __launch_bounds__(256) k_lg_tour(uint32_t A, uint32_t S, const uint32_t* __restrict__ arc_to, const uint32_t* __restrict__ arc_twin,
+                                                 const uint32_t* __restrict__ off, uint32_t* __restrict__ succ, int32_t* __restrict__ w0) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A) return;
+    uint32_t v = arc_to[i], j = arc_twin[i];
+    uint32_t nxt = (j + 1 < off[v + 1]) ? j + 1 : off[v];
+    if (nxt == off[S]) nxt = LG_NONE;
+    succ[i] = nxt; w0[i] = 1;
+}
+__global__ void __launch_bounds__(256) k_lg_parent(uint32_t A, uint32_t S, const uint32_t* __restrict__ arc_to, const uint32_t* __restrict__ arc_twin,
+                                                   const uint32_t* __restrict__ arc_e, const int32_t* __restrict__ w0, const uint32_t* __restrict__ erank,
+                                                   uint32_t* __restrict__ par, uint32_t* __restrict__ pkey, uint32_t* __restrict__ pedge) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { par[S] = S; pkey[S] = LG_NONE; pedge[S] = LG_NONE; }
+    if (i >= A) return;
+    uint32_t j = arc_twin[i];
+    if (w0[i] > w0[j]) {                       // crossed first in this direction: away from S
+        uint32_t c = arc_to[i];
+        par[c] = arc_to[j]; pkey[c] = erank[arc_e[i]]; pedge[c] = arc_e[i];
+    }
+}
+__global__ void __launch_bounds__(256) k_lg_lift0(uint32_t V, const uint32_t* __restrict__ par, const uint32_t* __restrict__ pkey,
+                                                  uint32_t* __restrict__ anc, uint32_t* __restrict__ mx) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    uint32_t p = par[v];
+    anc[v] = p; mx[v] = pkey[p];
+}
+__global__ void __launch_bounds__(256) k_lg_lift(uint32_t V, const uint32_t* __restrict__ anc, const uint32_t* __restrict__ mx,
+                                                 uint32_t* __restrict__ anc1, uint32_t* __restrict__ mx1) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    uint32_t a = anc[v];
+    anc1[v] = anc[a]; mx1[v] = max(mx[v], mx[a]);
+}
+// parent in T': the lower end of the nearest ancestor edge heavier than the own parent edge
+__global__ void __launch_bounds__(256) k_lg_tp(uint32_t L, uint32_t V, int K, const uint32_t* __restrict__ anc, const uint32_t* __restrict__ mx,
+                                               const uint32_t* __restrict__ pkey, uint64_t* __restrict__ skey, uint32_t* __restrict__ sval) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= L) return;
+    const uint32_t kv = pkey[v];
+    uint32_t cur = v;
+    for (int k = K - 1; k >= 0; --k) if (mx[(size_t)k * V + cur] < kv) cur = anc[(size_t)k * V + cur];
+    skey[v] = ((uint64_t)anc[cur] << 32) | (uint64_t)kv;
+    sval[v] = v;
+}
+__global__ void __launch_bounds__(256) k_lg_tarcs(uint32_t L, const uint64_t* __restrict__ sk, const uint32_t* __restrict__ sv,
+                                                  uint32_t* __restrict__ firstchild, uint32_t* __restrict__ succ) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L) return;
+    uint32_t v = sv[i], p = (uint32_t)(sk[i] >> 32);
+    if (i == 0 || (uint32_t)(sk[i - 1] >> 32) != p) firstchild[p] = v;
+    succ[2 * v + 1] = (i + 1 < L && (uint32_t)(sk[i + 1] >> 32) == p) ? 2 * sv[i + 1] : 2 * p + 1;
+}
+__global__ void __launch_bounds__(256) k_lg_tarcs2(uint32_t V, uint32_t S, const uint32_t* __restrict__ firstchild, uint32_t* __restrict__ succ,
+                                                   int32_t* __restrict__ w0) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    uint32_t fc = firstchild[v];
+    succ[2 * v] = fc != LG_NONE ? 2 * fc : 2 * v + 1;
+    w0[2 * v] = v != S ? 1 : 0; w0[2 * v + 1] = 0;
+    if (v == S) succ[2 * v + 1] = LG_NONE;
+}
+__global__ void __launch_bounds__(256) k_lg_pos(uint32_t L, const int32_t* __restrict__ w0, uint32_t* __restrict__ pos, int* __restrict__ bad) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= L) return;
+    int64_t t = (int64_t)L - (int64_t)w0[2 * v];
+    if (t < 0 || t >= (int64_t)L) { *bad = 1; t = 0; }
+    pos[v] = 1u + (uint32_t)t;
+}
+__global__ void __launch_bounds__(256) k_lg_final(uint32_t L, const uint32_t* __restrict__ pos, const uint32_t* __restrict__ pedge, const uint4* __restrict__ erec,
+                                                  const uint32_t* __restrict__ lake_root, uint32_t* __restrict__ flows, int32_t* __restrict__ dh,
+                                                  int32_t* __restrict__ indirection) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= L) return;
+    uint4 x = erec[pedge[v]];
+    uint32_t from = x.x == v ? x.z : x.w, to = x.x == v ? x.w : x.z;
+    uint32_t root = lake_root[v];
+    dh[root] = (int32_t)to;                    // 2098
+    indirection[root] = -(int32_t)from;        // 2103
+    flows[pos[v] - 1u] = root;                 // 2105
+}
+__global__ void __launch_bounds__(256) k_lg_pos_init(uint32_t V, uint32_t* __restrict__ pos) {
+    uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < V) pos[v] = v == V - 1 ? 0u : v + 1u;
+}
+
+// Returns VE_OK with *done = 1 when dh / indirection / flows of all L lakes have been written; *done = 0 asks the
+// caller for the serial growth (an equal-height group beyond LG_MAX_GROUP, or no fixed point within the round limit).
+static int lake_grow_parallel(ve_ctx* ctx, PassTable t, uint32_t cap, uint32_t n_cross, uint32_t L, const int32_t* dh0, const uint32_t* lrank,
+                              const uint32_t* lake_root, int32_t* dh, int32_t* indirection, uint32_t* flows, uint32_t* small, int* done) {
+    cudaStream_t st = ctx->stream;
+    *done = 0;
+    ctx->lake_rounds = 0;
+    const uint32_t V = L + 1, S = L;
+    int K = 1; while ((1ull << K) < (unsigned long long)V) ++K;
+    const size_t Mc = (size_t)n_cross + 1;
+    // ---- carve the work arrays
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    size_t eb = up(Mc * 8) * 3 + up(Mc * 4) * 6 + up(Mc * 16) * 2 + up(Mc) * 2;
+    uint8_t* E; VE_TRY(ve_scratch(ctx, 8, eb, (void**)&E));
+    uint8_t* q = E;
+    auto take = [&](size_t bytes) { uint8_t* r = q; q += up(bytes); return r; };
+    uint64_t* ehb_in = (uint64_t*)take(Mc * 8); uint64_t* ehb = (uint64_t*)take(Mc * 8); uint64_t* key_lo = (uint64_t*)take(Mc * 8);
+    uint32_t* idx_in = (uint32_t*)take(Mc * 4); uint32_t* idx_s = (uint32_t*)take(Mc * 4); uint32_t* gs = (uint32_t*)take(Mc * 4);
+    uint32_t* ge = (uint32_t*)take(Mc * 4); uint32_t* erank = (uint32_t*)take(Mc * 4); uint32_t* byrank = (uint32_t*)take(Mc * 4);
+    uint4* erec_in = (uint4*)take(Mc * 16); uint4* erec = (uint4*)take(Mc * 16);
+    uint8_t* obits = take(Mc); uint8_t* intree = take(Mc);
+    const size_t Vc = (size_t)V + 2, Ac = 2 * Vc;
+    size_t vb = up(Vc * 4) * (12 + 2 * (size_t)K) + up(Vc * 8) * 2 + up(Ac * 4) * 5;
+    uint8_t* W; VE_TRY(ve_scratch(ctx, 9, vb, (void**)&W));
+    q = W;
+    uint32_t* pos = (uint32_t*)take(Vc * 4); uint32_t* comp_a = (uint32_t*)take(Vc * 4); uint32_t* comp_b = (uint32_t*)take(Vc * 4);
+    uint32_t* best = (uint32_t*)take(Vc * 4); uint32_t* hook = (uint32_t*)take(Vc * 4); uint32_t* deg = (uint32_t*)take(Vc * 4);
+    uint32_t* off = (uint32_t*)take(Vc * 4); uint32_t* cur = (uint32_t*)take(Vc * 4); uint32_t* par = (uint32_t*)take(Vc * 4);
+    uint32_t* pkey = (uint32_t*)take(Vc * 4); uint32_t* pedge = (uint32_t*)take(Vc * 4); uint32_t* firstchild = (uint32_t*)take(Vc * 4);
+    uint32_t* anc = (uint32_t*)take(up(Vc * 4) * (size_t)K); uint32_t* mx = (uint32_t*)take(up(Vc * 4) * (size_t)K);
+    // anc / mx levels are addressed as k * V + v: pack them densely inside their blocks (K * V <= K * Vc)
+    uint64_t* skey = (uint64_t*)take(Vc * 8); uint64_t* skey_s = (uint64_t*)take(Vc * 8);
+    uint32_t* arc_to = (uint32_t*)take(Ac * 4); uint32_t* arc_twin = (uint32_t*)take(Ac * 4); uint32_t* arc_e = (uint32_t*)take(Ac * 4);
+    uint32_t* succ = (uint32_t*)take(Ac * 4); int32_t* w0 = (int32_t*)take(Ac * 4);
+    uint32_t* sval = cur;            // free after the arcs are filled
+    uint32_t* sval_s = deg;
+    // small: [16] edge counter, [17] toolarge, [18] changed, [19] bad, [20] boruvka comp selector, [32..95] round flags
+    VE_CUDA(cudaMemsetAsync(small + 16, 0, 16 * 4, st));
+    // ---- undirected passes, sorted by height once
+    k_lg_edges<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, t, dh0, lrank, L, small + 16, ehb_in, idx_in, erec_in);
+    VE_LAUNCH_CHECK();
+    uint32_t M = 0;
+    VE_CUDA(cudaMemcpyAsync(&M, small + 16, 4, cudaMemcpyDeviceToHost, st));
+    VE_CUDA(cudaStreamSynchronize(st));
+    if (M == 0 || M > n_cross) { ctx->err = "get_lakes: pass table inconsistent"; return VE_ERR_LAKE_GRAPH; }
+    const unsigned mb = ve_blocks(M, 256), vbk = ve_blocks(V, 256), lb = ve_blocks(L, 256);
+    size_t tmp_bytes = 0; void* tmp;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ehb_in, ehb, idx_in, idx_s, (int)M, 0, 64, st);
+    VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+    VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ehb_in, ehb, idx_in, idx_s, (int)M, 0, 64, st));
+    ctx->launches += 4;
+    k_lg_gather<<<mb, 256, 0, st>>>(M, idx_s, erec_in, erec);
+    VE_LAUNCH_CHECK();
+    k_lg_groups<<<mb, 256, 0, st>>>(M, ehb, gs, ge, (int*)(small + 17));
+    VE_LAUNCH_CHECK();
+    k_lg_pos_init<<<vbk, 256, 0, st>>>(V, pos);
+    VE_LAUNCH_CHECK();
+    int bor_bps = 0;
+    VE_TRY(ve_occupancy(ctx, (const void*)k_lg_boruvka, 256, 0, &bor_bps));
+    unsigned bor_grid = (unsigned)(bor_bps * ctx->sm_count);
+    { unsigned need = ve_blocks(std::max(M, V), 256); if (bor_grid > need) bor_grid = need; if (bor_grid < 1) bor_grid = 1; }
+    bool converged = false;
+    int round = 0;
+    for (; round < 12; ++round) {
+        k_lg_orient<<<mb, 256, 0, st>>>(M, erec, pos, gs, ge, obits, key_lo, round == 0 ? 1 : 0, (int*)(small + 18));
+        VE_LAUNCH_CHECK();
+        uint32_t hflag[4] = {0, 0, 0, 0};   // toolarge, changed, bad, sel
+        VE_CUDA(cudaMemcpyAsync(hflag, small + 17, 16, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        if (hflag[0]) return VE_OK;                                  // a huge equal-height group: serial path
+        if (hflag[2]) { ctx->err = "get_lakes: inconsistent lake graph (parallel growth)"; return VE_ERR_LAKE_GRAPH; }
+        if (round > 0 && !hflag[1]) { converged = true; break; }   // orientation repeated: the previous round's result stands
+        VE_CUDA(cudaMemsetAsync(small + 18, 0, 4, st));
+        k_lg_rank<<<mb, 256, 0, st>>>(M, gs, ge, key_lo, erank, byrank);
+        VE_LAUNCH_CHECK();
+        VE_CUDA(cudaMemsetAsync(small + 32, 0, 64 * 4, st));
+        {
+            uint32_t Mv = M, Vv = V; const uint4* er = erec; const uint32_t* rk = erank; const uint32_t* br = byrank;
+            uint32_t* fl = small + 32; uint32_t* sel = small + 20;
+            void* args[] = {(void*)&Mv, (void*)&Vv, (void*)&er, (void*)&rk, (void*)&br, (void*)&comp_a, (void*)&comp_b, (void*)&best,
+                            (void*)&hook, (void*)&intree, (void*)&fl, (void*)&sel};
+            VE_CUDA(cudaLaunchCooperativeKernel((void*)k_lg_boruvka, dim3(bor_grid), dim3(256), args, 0, st));
+            ctx->launches++;
+        }
+        uint32_t sel = 0;
+        VE_CUDA(cudaMemcpyAsync(&sel, small + 20, 4, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        const uint32_t* comp = sel ? comp_b : comp_a;
+        k_lg_check<<<vbk, 256, 0, st>>>(V, comp, (int*)(small + 21));
+        VE_LAUNCH_CHECK();
+        uint32_t disc = 0;
+        VE_CUDA(cudaMemcpyAsync(&disc, small + 21, 4, cudaMemcpyDeviceToHost, st));
+        VE_CUDA(cudaStreamSynchronize(st));
+        if (disc) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
+        // rooted spanning tree: parent and parent pass of every lake
+        VE_CUDA(cudaMemsetAsync(deg, 0, Vc * 4, st));
+        VE_CUDA(cudaMemsetAsync(cur, 0, Vc * 4, st));
+        k_lg_deg<<<mb, 256, 0, st>>>(M, erec, intree, deg);
+        VE_LAUNCH_CHECK();
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, deg, off, (int)(V + 1), st);
+        VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+        VE_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, deg, off, (int)(V + 1), st));
+        ctx->launches += 2;
+        k_lg_arcs<<<mb, 256, 0, st>>>(M, erec, intree, off, cur, arc_to, arc_twin, arc_e);
+        VE_LAUNCH_CHECK();
+        const uint32_t A = 2 * L;                                    // a spanning tree of V = L + 1 vertices
+        k_lg_tour<<<ve_blocks(A, 256), 256, 0, st>>>(A, S, arc_to, arc_twin, off, succ, w0);
+        VE_LAUNCH_CHECK();
+        VE_TRY(ve_list_rank(ctx, A, succ, w0, nullptr));
+        k_lg_parent<<<ve_blocks(A, 256), 256, 0, st>>>(A, S, arc_to, arc_twin, arc_e, w0, erank, par, pkey, pedge);
+        VE_LAUNCH_CHECK();
+        // T': nearest heavier ancestor edge by binary lifting
+        k_lg_lift0<<<vbk, 256, 0, st>>>(V, par, pkey, anc, mx);
+        VE_LAUNCH_CHECK();
+        for (int k = 0; k + 1 < K; ++k) {
+            k_lg_lift<<<vbk, 256, 0, st>>>(V, anc + (size_t)k * V, mx + (size_t)k * V, anc + (size_t)(k + 1) * V, mx + (size_t)(k + 1) * V);
+            VE_LAUNCH_CHECK();
+        }
+        k_lg_tp<<<lb, 256, 0, st>>>(L, V, K, anc, mx, pkey, skey, sval);
+        VE_LAUNCH_CHECK();
+        cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, skey, skey_s, sval, sval_s, (int)L, 0, 64, st);
+        VE_TRY(ve_cub_tmp(ctx, tmp_bytes, &tmp));
+        VE_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, skey, skey_s, sval, sval_s, (int)L, 0, 64, st));
+        ctx->launches += 4;
+        VE_CUDA(cudaMemsetAsync(firstchild, 0xff, Vc * 4, st));
+        k_lg_tarcs<<<lb, 256, 0, st>>>(L, skey_s, sval_s, firstchild, succ);
+        VE_LAUNCH_CHECK();
+        k_lg_tarcs2<<<vbk, 256, 0, st>>>(V, S, firstchild, succ, w0);
+        VE_LAUNCH_CHECK();
+        VE_TRY(ve_list_rank(ctx, 2 * V, succ, w0, nullptr));
+        k_lg_pos<<<lb, 256, 0, st>>>(L, w0, pos, (int*)(small + 19));
+        VE_LAUNCH_CHECK();
+    }
+    if (!converged) return VE_OK;                                     // no fixed point within the limit: serial path
+    ctx->lake_rounds = (uint32_t)round;
+    k_lg_final<<<lb, 256, 0, st>>>(L, pos, pedge, erec, lake_root, flows, dh, indirection);
+    VE_LAUNCH_CHECK();
+    *done = 1;
+    return VE_OK;
+}
+
 // ---- (v) per-lake flood -----------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_lake_fill(Geom g, uint32_t n_flows, const uint32_t* __restrict__ flows,
                                                    const double* __restrict__ h, const uint32_t* __restrict__ root,
@@ -651,7 +1032,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     if (hs[9]) { ctx->err = "get_lakes: tree depth overflow"; return VE_ERR_TOO_LARGE; }
     uint32_t n_flows = 0;
     uint32_t *flows = nullptr, *outflow = nullptr;
-    VE_TRY(ve_scratch(ctx, 5, ((size_t)n_lakes + 1) * 4 * 2, (void**)&flows));
+    VE_TRY(ve_scratch(ctx, 5, ((size_t)n_lakes + 1) * 4 * 3, (void**)&flows));
     outflow = flows + n_lakes + 1;
     if (n_lakes > 0) {
         uint32_t cap = 64;
@@ -661,10 +1042,31 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         t.key = (uint64_t*)tbl; t.hb = (unsigned long long*)(tbl + (size_t)cap * 8);
         t.tie = (unsigned long long*)(tbl + (size_t)cap * 16); t.edge = (uint64_t*)(tbl + (size_t)cap * 24);
         t.mask = cap - 1;
-        VE_CUDA(cudaMemsetAsync(t.key, 0, (size_t)cap * 8, st));
-        VE_CUDA(cudaMemsetAsync(t.hb, 0xff, (size_t)cap * 16, st)); // hb and tie = max
-        for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
+        auto build_table = [&]() -> int {
+            VE_CUDA(cudaMemsetAsync(t.key, 0, (size_t)cap * 8, st));
+            VE_CUDA(cudaMemsetAsync(t.hb, 0xff, (size_t)cap * 16, st)); // hb and tie = max
+            for (int mode = 1; mode <= 3; ++mode) { k_pass_scan<<<nb, 256, 0, st>>>(g, mode, h, dh0, root, bfskey, t, small + 2); VE_LAUNCH_CHECK(); }
+            return VE_OK;
+        };
+        VE_TRY(build_table());
         pc.mark("pass table");
+        // (iii)/(iv): parallel growth; the one-warp heap of round 1 stays as the path for degenerate inputs
+        // (a giant equal-height group, no fixed point within the round limit) and behind ve_set_debug("lakes_serial")
+        int grown = 0;
+        if (!ctx->dbg_lakes_serial) {
+            uint32_t* lake_root_p = outflow + n_lakes + 1;
+            k_lake_roots<<<nb, 256, 0, st>>>(n, dh0, lrank, lake_root_p);
+            VE_LAUNCH_CHECK();
+            VE_TRY(lake_grow_parallel(ctx, t, cap, n_cross, n_lakes, dh0, lrank, lake_root_p, dh, indirection, flows, small, &grown));
+            if (grown) { n_flows = n_lakes; pc.mark("growth (parallel)"); }
+            else {   // the growth's list ranking may have recycled the table's memory
+                VE_TRY(ve_scratch(ctx, 6, (size_t)cap * 32, (void**)&tbl));
+                t.key = (uint64_t*)tbl; t.hb = (unsigned long long*)(tbl + (size_t)cap * 8);
+                t.tie = (unsigned long long*)(tbl + (size_t)cap * 16); t.edge = (uint64_t*)(tbl + (size_t)cap * 24);
+                VE_TRY(build_table());
+            }
+        }
+        if (!grown) {
         // adjacency (CSR over non-boundary lakes)
         uint32_t *deg, *off, *lake_root, *adj_tgt, *cidx, *cidx2; uint64_t *adj_ft, *adj_k0, *ck0, *ck1, *ck0s, *ck1s; uint4 *cand_pl, *cand_pl_s;
         size_t lk = (size_t)n_lakes + 1;
@@ -740,6 +1142,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         if (pc.on) fprintf(stderr, "[lakes] lakes %u cand %u pops %u pushes %u; kcycles sift %u scan %u push %u\n", n_lakes, n_cand, cstat[1], cstat[2], cstat[3], cstat[4], cstat[5]);
         if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
         pc.mark("connect");
+        }
         // (v) flood: per-lake stacks carved out of one array by an exclusive scan of tree sizes
         k_save_outflow<<<ve_blocks(n_flows, 256), 256, 0, st>>>(n_flows, flows, dh, outflow);
         VE_LAUNCH_CHECK();
