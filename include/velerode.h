@@ -96,6 +96,19 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
 void ve_destroy(ve_ctx* ctx);
 const char* ve_last_error(ve_ctx* ctx);
 
+/* Row-band sharding of ONE map over several GPUs, one process (rank) per GPU (no counterpart in the
+ * single-threaded reference).  Every rank creates its own context for the same map on its own device, loads the
+ * same inputs, then calls ve_mg_attach with an all-gather supplied by the host (MPI, torch.distributed, ...):
+ * cb(user, send, recv, bytes) must deliver every rank's `bytes` bytes, in rank order, into recv on every rank;
+ * bytes == 0 is a plain barrier.  The library uses it once to exchange CUDA IPC handles and afterwards as the
+ * barrier between sweeps.  From then on ve_step / ve_run* must be called collectively (same calls, same order) on
+ * all ranks; every rank ends every step with the complete, identical state.  Sharded today: the Gauss-Seidel
+ * sweeps (erosion.rs:1127-1151, 1237-1450): rank r solves the nodes of rows [r*ny/world, (r+1)*ny/world) and reads the
+ * values of nodes in other bands directly from their owner's memory over NVLink; every other stage runs
+ * replicated.  world must be a power of two <= 8. */
+typedef void (*ve_allgather_cb)(void* user, const void* send, void* recv, size_t bytes);
+int ve_mg_attach(ve_ctx* ctx, int rank, int world, ve_allgather_cb cb, void* user);
+
 /* Test and tuning knobs (no counterpart in the reference; defaults are what production uses).  Keys:
  * "lanes_up" / "lanes_down" / "lanes_other" (k > 1: thread-per-node sweeps), "df_bps" (resident blocks per SM
  * of the sweeps), "newton" (bit 0: skip the Newton loop, bit 2: force the slow re-solve), "newton_variant",

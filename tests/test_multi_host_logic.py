@@ -51,3 +51,15 @@ def test_single_process_identity():
     from veloren_b200 import multi
     v, ms = multi.aggregate_mcell_iters_per_s(1000, 3, 2.0)
     assert ms == 2.0 and v == 1000 * 3 / 2e-3 / 1e6
+
+
+def test_row_band_ownership():
+    from veloren_b200 import multi
+    n, ny = 1 << 20, 1 << 10
+    for world in (1, 2, 4, 8):
+        per = n // world
+        assert multi.band_of_cell(0, n, world) == 0 and multi.band_of_cell(n - 1, n, world) == world - 1
+        for r in range(world):
+            lo, hi = multi.band_rows(r, ny, world)
+            assert multi.band_of_cell(lo * 1024, n, world) == r and multi.band_of_cell(hi * 1024 - 1, n, world) == r
+            assert (hi - lo) * 1024 == per

@@ -89,6 +89,39 @@ template <class T> __global__ void k_to_stack_index(uint32_t n, const T* __restr
     if (i < n) o[stackpos[i]] = a[i];
 }
 
+// ---- row bands over several GPUs ----------------------------------------------------------------------
+int ve_mg_barrier(ve_ctx* ctx) {
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->mg_world > 1) ctx->mg_cb(ctx->mg_user, nullptr, nullptr, 0);
+    return VE_OK;
+}
+int ve_mg_gather(ve_ctx* ctx, void* local, size_t elem_bytes) {
+    if (ctx->mg_world <= 1) return VE_OK;
+    auto it = ctx->mg_peers.find((const void*)local);
+    if (it == ctx->mg_peers.end()) { ctx->err = "ve_mg_gather: array is not shared"; return VE_ERR_INVALID; }
+    const size_t band = ((size_t)ctx->g.n >> 0) / (size_t)ctx->mg_world * elem_bytes;
+    for (int r = 0; r < ctx->mg_world; ++r) {
+        if (r == ctx->mg_rank) continue;
+        VE_CUDA(cudaMemcpyAsync((char*)local + band * r, (const char*)it->second[r] + band * r, band, cudaMemcpyDefault, ctx->stream));
+    }
+    return VE_OK;
+}
+static int mg_share(ve_ctx* ctx, void* local) {
+    const int W = ctx->mg_world;
+    cudaIpcMemHandle_t mine;
+    VE_CUDA(cudaIpcGetMemHandle(&mine, local));
+    std::vector<cudaIpcMemHandle_t> all(W);
+    ctx->mg_cb(ctx->mg_user, &mine, all.data(), sizeof(cudaIpcMemHandle_t));
+    std::vector<void*> ptrs(8, nullptr);
+    for (int r = 0; r < W; ++r) {
+        if (r == ctx->mg_rank) { ptrs[r] = local; continue; }
+        void* p = nullptr;
+        VE_CUDA(cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        ptrs[r] = p;
+    }
+    ctx->mg_peers[(const void*)local] = ptrs;
+    return VE_OK;
+}
 extern "C" {
 
 void ve_default_params(ve_params* p) {
@@ -164,6 +197,8 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
     ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0;
+    ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
+    ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
     ctx->hist_count = 0;
     ctx->up_ev_ready = false; ctx->up_ms_total = 0.0; ctx->up_launches_total = 0;
@@ -184,6 +219,11 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (auto& kv : ctx->mg_peers)
+        for (int r = 0; r < ctx->mg_world; ++r) if (r != ctx->mg_rank && kv.second[r]) cudaIpcCloseMemHandle(kv.second[r]);
+    if (ctx->mg_uw_flag) cudaFree(ctx->mg_uw_flag);
+    if (ctx->mg_uw_val) cudaFree(ctx->mg_uw_val);
+    if (ctx->mg_errsq) cudaFree(ctx->mg_errsq);
     if (ctx->up_ev_ready) for (int i = 0; i < 200; ++i) cudaEventDestroy(ctx->up_ev[i]);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->noise_host) cudaFreeHost(ctx->noise_host);
@@ -192,6 +232,27 @@ void ve_destroy(ve_ctx* ctx) {
 }
 
 const char* ve_last_error(ve_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int ve_mg_attach(ve_ctx* ctx, int rank, int world, ve_allgather_cb cb, void* user) {
+    if (!ctx || !cb || world < 1 || world > 8 || (world & (world - 1)) || rank < 0 || rank >= world) return VE_ERR_INVALID;
+    if (ctx->mg_world > 1) { ctx->err = "ve_mg_attach: already attached"; return VE_ERR_INVALID; }
+    if (world == 1) return VE_OK;
+    if (ctx->g.n / (uint32_t)world < 1024u) { ctx->err = "ve_mg_attach: map too small for this many bands"; return VE_ERR_INVALID; }
+    if (ctx->lanes_down != 1 || ctx->lanes_up != 1) { ctx->err = "ve_mg_attach: needs the warp-per-node sweeps"; return VE_ERR_INVALID; }
+    VE_CUDA(cudaSetDevice(ctx->device));
+    ctx->mg_rank = rank; ctx->mg_world = world; ctx->mg_cb = cb; ctx->mg_user = user;
+    uint32_t per = ctx->g.n / (uint32_t)world, sh = 0;
+    while ((1u << sh) < per) ++sh;
+    ctx->mg_shift = sh;
+    const size_t n = ctx->g.n;
+    VE_CUDA(cudaMalloc((void**)&ctx->mg_uw_flag, n));
+    VE_CUDA(cudaMalloc((void**)&ctx->mg_uw_val, n * 8));
+    VE_CUDA(cudaMalloc((void**)&ctx->mg_errsq, n * 8 + 1024 * 8 + 256));
+    void* shared[] = {ctx->deltah, ctx->h_new, ctx->wh, ctx->wh_prev, ctx->sill_cur, ctx->sill_prev, ctx->lake_silt,
+                      ctx->mg_uw_flag, ctx->mg_uw_val, ctx->mg_errsq};
+    for (void* a : shared) VE_TRY(mg_share(ctx, a));
+    return ve_mg_barrier(ctx);
+}
 
 int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     if (!ctx || !key) return VE_ERR_INVALID;

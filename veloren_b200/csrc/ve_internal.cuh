@@ -28,6 +28,10 @@ enum VeTimer {
     VT_BASEMENT, VT_THERMAL, VT_DIFFUSION, VT_TOTAL, VT_COUNT
 };
 
+// Multi-GPU (row bands): cell i belongs to rank i >> shift; p[r] is rank r's copy of the array (its own band is
+// the authoritative part).  With one GPU every entry is the local array and shift = 31.
+template <class T> struct Remote { T* p[8]; uint32_t shift; };
+
 struct NoiseDev {
     uint32_t octaves;
     double frequency, lacunarity, persistence, scale_factor;
@@ -104,6 +108,11 @@ struct ve_ctx {
     double up_ms_total; uint64_t up_launches_total;
     // per-step history since ve_create (ring of the last 256 steps): Gauss-Seidel iterations and lake counts
     int hist_n_gs[256]; uint32_t hist_n_lakes[256]; uint64_t hist_count;
+    // row-band sharding of the Gauss-Seidel sweeps over several GPUs (ve_mg_attach); world == 1: off
+    int mg_rank, mg_world; uint32_t mg_shift;
+    ve_allgather_cb mg_cb; void* mg_user;
+    std::map<const void*, std::vector<void*>> mg_peers;     // local base pointer -> every rank's base pointer
+    uint8_t* mg_uw_flag; double* mg_uw_val; double* mg_errsq; // sweep outputs that live in scratch on one GPU
     // last-step scalars
     int n_gs; double gs_err; double maxh; uint64_t boundary_len; uint32_t n_lakes; uint32_t n_underwater;
 };
@@ -135,6 +144,19 @@ static inline unsigned ve_blocks(uint64_t n, unsigned bs) { return (unsigned)((n
 
 // resident blocks per SM of `func` at this block size / dynamic shared memory, cached per context; the
 // >48 KB shared-memory opt-in is made per device
+// multi-GPU helpers (ve_api.cu): every rank's pointer of a shared array, host barrier, band gather
+template <class T> static inline Remote<T> ve_remote(const ve_ctx* ctx, T* local) {
+    Remote<T> r;
+    for (int i = 0; i < 8; ++i) r.p[i] = local;
+    r.shift = 31u;
+    if (ctx->mg_world > 1) {
+        auto it = ctx->mg_peers.find((const void*)local);
+        if (it != ctx->mg_peers.end()) { for (int i = 0; i < ctx->mg_world; ++i) r.p[i] = (T*)it->second[i]; r.shift = ctx->mg_shift; }
+    }
+    return r;
+}
+int ve_mg_barrier(ve_ctx* ctx);                                   // stream sync + all ranks arrive
+int ve_mg_gather(ve_ctx* ctx, void* local, size_t elem_bytes);    // copy the other ranks' bands into the local replica
 int ve_occupancy(ve_ctx* ctx, const void* func, int block, size_t smem, int* bps_out);
 uint64_t ve_spin_limit_ns(const ve_ctx* ctx);
 // scratch buffer i with at least `bytes` bytes (grown on demand; contents undefined)

@@ -26,7 +26,7 @@ SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_
            "up_launches_total", "lake_rounds"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
-           "ve_set_noise_cb", "ve_set_debug", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
+           "ve_set_noise_cb", "ve_mg_attach", "ve_set_debug", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_get_history", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
@@ -58,6 +58,7 @@ RIVER_DTYPE = np.dtype([("velocity", np.float32, 3), ("spline_derivative", np.fl
                         ("aux", np.uint32, 2)])   # ve_river
 
 PROGRESS_CB = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_double)
+ALLGATHER_CB = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)   # ve_allgather_cb
 
 
 def build():
@@ -127,6 +128,33 @@ class ErosionContext:
         for k, v in kw.items():
             setattr(prm, k, float(v))
         self._chk(lib().ve_set_params(self.ctx, ctypes.byref(prm)))
+
+    def attach_multi(self, rank, world, allgather=None, barrier=None, group=None):
+        """ve_mg_attach: shard this map's Gauss-Seidel sweeps as row bands over `world` GPUs (one process per GPU;
+        every rank holds a context for the same map with the same inputs and makes the same calls from here on).
+        allgather(bytes) -> list of every rank's bytes and barrier() default to torch.distributed on `group`
+        (a gloo group is the natural choice: this is the control plane, the data moves over NVLink)."""
+        if allgather is None or barrier is None:
+            import torch.distributed as dist
+
+            def allgather(b, _g=group):
+                out = [None] * world
+                dist.all_gather_object(out, b, group=_g)
+                return out
+
+            def barrier(_g=group):
+                dist.barrier(group=_g)
+
+        def tramp(_user, send, recv, nbytes):
+            if nbytes == 0:
+                barrier()
+                return
+            parts = allgather(ctypes.string_at(send, nbytes))
+            for i, part in enumerate(parts):
+                ctypes.memmove(recv + i * nbytes, part, nbytes)
+
+        self._mg_cb = ALLGATHER_CB(tramp)                  # keep the trampoline alive
+        self._chk(lib().ve_mg_attach(self.ctx, int(rank), int(world), self._mg_cb, None))
 
     def set_debug(self, **kw):
         """Test / tuning knobs of ve_set_debug (lanes_up=8, newton=4, spin_limit_ms=200, ...)."""

@@ -8,6 +8,20 @@ communication is a barrier and a max-reduce of the per-rank device time.
 import torch
 import torch.distributed as dist
 
+
+
+def band_of_cell(cell, n_cells, world):
+    """Row-band ownership used by ve_mg_attach: cells are row-major, rank r owns the contiguous range
+    [r * n/world, (r+1) * n/world), i.e. rows [r * ny/world, (r+1) * ny/world)."""
+    per = n_cells // world
+    return cell // per
+
+
+def band_rows(rank, ny, world):
+    per = ny // world
+    return rank * per, (rank + 1) * per
+
+
 BASE_SEED = 130626853  # DEFAULT_WORLD_SEED, world/src/sim/mod.rs:586
 
 
