@@ -151,6 +151,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"            # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # every rank erodes its own copy of the same world (same seed: efficiency then measures the machine,
     # not the world), inputs resident before timing
@@ -238,6 +239,37 @@ def run_ours(args):
                 "f32_round_trip_ok": bool(np.array_equal(h2, hf.astype(np.float32).astype(np.float64))),
                 "checksum_h": float(hf.sum())}
 
+    # ---- N > 1: BASELINE configs[2], ONE 2048x2048 world sharded as row bands over the N ranks (ve_mg_attach; strong
+    # scaling), next to the same world on one GPU measured by rank 0 in the same run ---------------------------------
+    row_bands = None
+    if world > 1 and not args.no_row_bands:
+        ctl = dist.new_group(backend="gloo")              # control plane (IPC handles, barriers); data moves over NVLink
+        f3 = synth.generate(11, 11)
+        c3 = ErosionContext(11, 11, device=local)
+        c3.configure(f3)
+        c3.attach_multi(rank, world, group=ctl)
+        c3.run_device(3)
+        barrier()
+        ms3 = multi.max_over_ranks(c3.run_device_timed(5), device="cuda")
+        chk3 = float(c3.get("h").sum())
+        c3.close()
+        barrier()
+        ms31 = None
+        if rank == 0:
+            c31 = ErosionContext(11, 11, device=local)
+            c31.configure(f3)
+            c31.run_device(3)
+            ms31 = c31.run_device_timed(5)
+            same = float(c31.get("h").sum()) == chk3
+            c31.close()
+            row_bands = {"workload": "BASELINE configs[2]: one 2048x2048 world, row bands over %d GPUs" % world, "scaling": "strong",
+                         "steps": 5, "warmup": 3, "ms_per_step": ms3 / 5, "mcell_iters_per_s": (1 << 22) * 5 / (ms3 * 1e-3) / 1e6,
+                         "one_gpu_ms_per_step": ms31 / 5, "speedup_vs_one_gpu": ms31 / ms3, "identical_to_one_gpu": same,
+                         "sharded": "Gauss-Seidel sweeps (erosion.rs:1127-1151, 1237-1450): owner-computes per band, other bands' "
+                                    "words polled over NVLink (CUDA IPC peer memory)",
+                         "replicated": "every other stage (dependency-depth bound at this size: DESIGN.md section 8)"}
+        barrier()
+
     # ---- CPU baseline on the box's host cores (rank 0, N=1 only): bounded sample ---------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -259,7 +291,7 @@ def run_ours(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": int(launches), "clocks": clocks, "per_rank": per_rank,
-                "full_do_erosion": full,
+                "full_do_erosion": full, "row_bands": row_bands,
                 "full_do_erosion_estimate_s": ms_max / args.steps * 100 / 1e3}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -274,6 +306,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-full", action="store_true", help="skip the measured 100-step do_erosion run")
+    ap.add_argument("--no-row-bands", action="store_true", help="N > 1: skip the sharded 2048x2048 measurement")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

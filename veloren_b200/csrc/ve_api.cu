@@ -198,7 +198,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
     ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
-    ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr;
+    ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
     ctx->hist_count = 0;
     ctx->up_ev_ready = false; ctx->up_ms_total = 0.0; ctx->up_launches_total = 0;
@@ -224,6 +224,7 @@ void ve_destroy(ve_ctx* ctx) {
     if (ctx->mg_uw_flag) cudaFree(ctx->mg_uw_flag);
     if (ctx->mg_uw_val) cudaFree(ctx->mg_uw_val);
     if (ctx->mg_errsq) cudaFree(ctx->mg_errsq);
+    if (ctx->mg_order_own) cudaFree(ctx->mg_order_own);
     if (ctx->up_ev_ready) for (int i = 0; i < 200; ++i) cudaEventDestroy(ctx->up_ev[i]);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->noise_host) cudaFreeHost(ctx->noise_host);
@@ -248,6 +249,7 @@ int ve_mg_attach(ve_ctx* ctx, int rank, int world, ve_allgather_cb cb, void* use
     VE_CUDA(cudaMalloc((void**)&ctx->mg_uw_flag, n));
     VE_CUDA(cudaMalloc((void**)&ctx->mg_uw_val, n * 8));
     VE_CUDA(cudaMalloc((void**)&ctx->mg_errsq, n * 8 + 1024 * 8 + 256));
+    VE_CUDA(cudaMalloc((void**)&ctx->mg_order_own, n * 4 + 256));
     void* shared[] = {ctx->deltah, ctx->h_new, ctx->wh, ctx->wh_prev, ctx->sill_cur, ctx->sill_prev, ctx->lake_silt,
                       ctx->mg_uw_flag, ctx->mg_uw_val, ctx->mg_errsq};
     for (void* a : shared) VE_TRY(mg_share(ctx, a));

@@ -113,6 +113,7 @@ struct ve_ctx {
     ve_allgather_cb mg_cb; void* mg_user;
     std::map<const void*, std::vector<void*>> mg_peers;     // local base pointer -> every rank's base pointer
     uint8_t* mg_uw_flag; double* mg_uw_val; double* mg_errsq; // sweep outputs that live in scratch on one GPU
+    uint32_t* mg_order_own;                                   // order_bu restricted to this rank's band (n / world entries)
     // last-step scalars
     int n_gs; double gs_err; double maxh; uint64_t boundary_len; uint32_t n_lakes; uint32_t n_underwater;
 };
