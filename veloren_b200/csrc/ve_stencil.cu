@@ -5,51 +5,69 @@
 
 // ---------------------------------------------------------------------------------------------
 // E1: D8 receivers.  util.rs:251-279; ocean predicate of erosion.rs:818 when use_h_le0 != 0.
-__global__ void __launch_bounds__(256) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
-                                                  int use_h_le0, int32_t* __restrict__ dh) {
-    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (posi >= g.n) return;
-    double nh = h[posi];
+// E1 and E3b/c read the 3x3 neighbourhood of one f64 field: a CTA stages its 32x8 tile plus a one-cell halo in
+// shared memory (coalesced rows, every value fetched from L2/HBM once per CTA instead of up to nine times) and
+// the stencil runs out of shared memory.  Cells outside the map hold `pad`, chosen so that the reference's
+// in-bounds test needs no branch: +inf is never a lower neighbour, NaN compares false both ways.
+#define VE_TX 32
+#define VE_TY 8
+__device__ __forceinline__ void stage_tile(const Geom& g, const double* __restrict__ a, double pad, double (*s)[VE_TX + 2]) {
+    const int x0 = (int)blockIdx.x * VE_TX - 1, y0 = (int)blockIdx.y * VE_TY - 1;
+    for (int i = (int)threadIdx.x; i < (VE_TX + 2) * (VE_TY + 2); i += VE_TX * VE_TY) {
+        const int ty = i / (VE_TX + 2), tx = i - ty * (VE_TX + 2);
+        const int x = x0 + tx, y = y0 + ty;
+        s[ty][tx] = g.inb(x, y) ? a[g.idx(x, y)] : pad;
+    }
+    __syncthreads();
+}
+__global__ void __launch_bounds__(VE_TX * VE_TY) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
+                                                            int use_h_le0, int32_t* __restrict__ dh) {
+    __shared__ double s[VE_TY + 2][VE_TX + 2];
+    stage_tile(g, h, INFINITY, s);
+    const int lx = (int)(threadIdx.x % VE_TX), ly = (int)(threadIdx.x / VE_TX);
+    const int x = (int)blockIdx.x * VE_TX + lx, y = (int)blockIdx.y * VE_TY + ly;
+    if (x >= g.nx || y >= g.ny) return;
+    const uint32_t posi = g.idx(x, y);
+    double nh = s[ly + 1][lx + 1];
     bool oc = ocean[posi] != 0;
     if (use_h_le0) oc = oc && (nh <= 0.0);
     if (oc) { dh[posi] = -2; return; }
-    int x = g.x_of(posi), y = g.y_of(posi);
     int best = -1; double besth = nh;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        int xx = x + c_ndx[k], yy = y + c_ndy[k];
-        if (!g.inb(xx, yy)) continue;
-        uint32_t np = g.idx(xx, yy);
-        double nbh = h[np];
-        if (nbh < besth) { besth = nbh; best = (int)np; }
+        double nbh = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
+        if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
     }
     dh[posi] = best;
 }
 
+static inline dim3 ve_tile_grid(const Geom& g) { return dim3((unsigned)((g.nx + VE_TX - 1) / VE_TX), (unsigned)((g.ny + VE_TY - 1) / VE_TY)); }
+
 int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh) {
-    k_downhill<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
+    k_downhill<<<ve_tile_grid(ctx->g), VE_TX * VE_TY, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
 // E3b/E3c: receiver mask, donor count and MFD weights.  erosion.rs:2407-2439, 2444-2479.
-__global__ void __launch_bounds__(256) k_mrec(Geom g, const double* __restrict__ wh, uint8_t* __restrict__ mrec,
-                                              uint8_t* __restrict__ ndon, double* __restrict__ mwrec) {
-    uint32_t ij = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ij >= g.n) return;
+__global__ void __launch_bounds__(VE_TX * VE_TY) k_mrec(Geom g, const double* __restrict__ wh, uint8_t* __restrict__ mrec,
+                                                        uint8_t* __restrict__ ndon, double* __restrict__ mwrec) {
+    __shared__ double s[VE_TY + 2][VE_TX + 2];
+    stage_tile(g, wh, __longlong_as_double(0x7ff8000000000000LL), s);
+    const int lx = (int)(threadIdx.x % VE_TX), ly = (int)(threadIdx.x / VE_TX);
+    const int x = (int)blockIdx.x * VE_TX + lx, y = (int)blockIdx.y * VE_TY + ly;
+    if (x >= g.nx || y >= g.ny) return;
+    const uint32_t ij = g.idx(x, y);
     const double SQ = vm_sqrt(32.0 * 32.0 + 32.0 * 32.0);
-    double wh_ij = wh[ij];
-    int x = g.x_of(ij), y = g.y_of(ij);
+    double wh_ij = s[ly + 1][lx + 1];
     unsigned mr = 0, nd = 0;
     double wrec[8];
     double sumweight = 0.0; int nrec = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         wrec[k] = 0.0;
-        int xx = x + c_ndx[k], yy = y + c_ndy[k];
-        if (!g.inb(xx, yy)) continue;
-        double wh_ijk = wh[g.idx(xx, yy)];
+        double wh_ijk = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];      // NaN outside the map: neither branch is taken
         if (wh_ij > wh_ijk) {
             mr |= 1u << k;
             double lrec = (c_ndx[k] != 0 && c_ndy[k] != 0) ? SQ : 32.0;
@@ -76,7 +94,7 @@ __global__ void __launch_bounds__(256) k_mrec(Geom g, const double* __restrict__
 }
 
 int ve_k_mrec(ve_ctx* ctx) {
-    k_mrec<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->wh, ctx->mrec, ctx->ndon, ctx->mwrec);
+    k_mrec<<<ve_tile_grid(ctx->g), VE_TX * VE_TY, 0, ctx->stream>>>(ctx->g, ctx->wh, ctx->mrec, ctx->ndon, ctx->mwrec);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
@@ -248,15 +266,18 @@ __global__ void __launch_bounds__(256) k_kfactors(Geom g, ve_params P, float max
         double ms_pow = vm_pow(ms, q_);
         unsigned mr = mrec[posi];
         const double* w = mwrec + (size_t)posi * 8;
+        // the neighbour distance takes two values: its powers are evaluated once per cell, not once per receiver
+        // (same arguments, same function: same bits)
+        const double nd_n_s = vm_pow(32.0, n), nd_n_d = vm_pow(SQ, n), nd_q_s = vm_pow(32.0, q_), nd_q_d = vm_pow(SQ, q_);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
             if (!((mr >> kk) & 1u)) continue;
             double wk = w[kk];
-            double nd = (c_ndx[kk] != 0 && c_ndy[kk] != 0) ? SQ : 32.0;
-            double knew = kk_ * vm_pow(p * chunk_area * (area_i * wk), m) / vm_pow(nd, n);
+            const bool diag = (c_ndx[kk] != 0 && c_ndy[kk] != 0);
+            double knew = kk_ * vm_pow(p * chunk_area * (area_i * wk), m) / (diag ? nd_n_d : nd_n_s);
             fs[kk] = (float)knew;
             double k = (wk * (uplift_i + (double)max_uplift * g_i / p)) / (1.0 + k_da * vm_pow(wk * 0.1e6, q)) / ms_pow;
-            double knew2 = k * (1.0 + k_da * P.chunk_area_pow_q * vm_pow(area_i * wk, q)) / vm_pow(nd, q_);
+            double knew2 = k * (1.0 + k_da * P.chunk_area_pow_q * vm_pow(area_i * wk, q)) / (diag ? nd_q_d : nd_q_s);
             df[kk] = (float)knew2;
         }
     }
