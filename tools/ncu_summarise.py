@@ -12,9 +12,9 @@ def num(r, name):
     try: return float(v)
     except ValueError: return None
 def short(n):
-    n = re.sub(r"\(.*", "", n)
-    m = re.match(r"(?:void )?(k_\w+)(?:<(\w+)(?:<\(bool\)(\d)>)?)?", n)
-    if m: return m.group(1) + ("<%s%s>" % (m.group(2), "" if m.group(3) in (None, "0") else ",MG") if m.group(2) else "")
+    n = re.sub(r"\((?!bool).*", "", n)
+    m = re.match(r"(?:void )?(k_\w+)(?:<(\w+))?", n)
+    if m: return m.group(1) + ("<%s>" % m.group(2) if m.group(2) else "")
     return n[:60]
 units = {n: rows[1][i] for n, i in col.items()}
 def to_bytes(r, name):

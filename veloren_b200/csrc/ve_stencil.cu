@@ -10,91 +10,101 @@
 // the stencil runs out of shared memory.  Cells outside the map hold `pad`, chosen so that the reference's
 // in-bounds test needs no branch: +inf is never a lower neighbour, NaN compares false both ways.
 #define VE_TX 32
-#define VE_TY 8
+#define VE_TY 32          /* rows per CTA tile; VE_TR rows of threads walk them (several loads in flight per thread) */
+#define VE_TR 8
 __device__ __forceinline__ void stage_tile(const Geom& g, const double* __restrict__ a, double pad, double (*s)[VE_TX + 2]) {
     const int x0 = (int)blockIdx.x * VE_TX - 1, y0 = (int)blockIdx.y * VE_TY - 1;
-    for (int i = (int)threadIdx.x; i < (VE_TX + 2) * (VE_TY + 2); i += VE_TX * VE_TY) {
+#pragma unroll 5
+    for (int i = (int)threadIdx.x; i < (VE_TX + 2) * (VE_TY + 2); i += VE_TX * VE_TR) {
         const int ty = i / (VE_TX + 2), tx = i - ty * (VE_TX + 2);
         const int x = x0 + tx, y = y0 + ty;
         s[ty][tx] = g.inb(x, y) ? a[g.idx(x, y)] : pad;
     }
     __syncthreads();
 }
-__global__ void __launch_bounds__(VE_TX * VE_TY) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
+__global__ void __launch_bounds__(VE_TX * VE_TR) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
                                                             int use_h_le0, int32_t* __restrict__ dh) {
     __shared__ double s[VE_TY + 2][VE_TX + 2];
     stage_tile(g, h, INFINITY, s);
-    const int lx = (int)(threadIdx.x % VE_TX), ly = (int)(threadIdx.x / VE_TX);
-    const int x = (int)blockIdx.x * VE_TX + lx, y = (int)blockIdx.y * VE_TY + ly;
-    if (x >= g.nx || y >= g.ny) return;
-    const uint32_t posi = g.idx(x, y);
-    double nh = s[ly + 1][lx + 1];
-    bool oc = ocean[posi] != 0;
-    if (use_h_le0) oc = oc && (nh <= 0.0);
-    if (oc) { dh[posi] = -2; return; }
-    int best = -1; double besth = nh;
+    const int lx = (int)(threadIdx.x % VE_TX);
+    const int x = (int)blockIdx.x * VE_TX + lx;
+    if (x >= g.nx) return;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        double nbh = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
-        if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
+    for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
+        const int y = (int)blockIdx.y * VE_TY + ly;
+        if (y >= g.ny) break;
+        const uint32_t posi = g.idx(x, y);
+        double nh = s[ly + 1][lx + 1];
+        bool oc = ocean[posi] != 0;
+        if (use_h_le0) oc = oc && (nh <= 0.0);
+        int best = -1; double besth = nh;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            double nbh = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
+            if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
+        }
+        dh[posi] = oc ? -2 : best;
     }
-    dh[posi] = best;
 }
 
 static inline dim3 ve_tile_grid(const Geom& g) { return dim3((unsigned)((g.nx + VE_TX - 1) / VE_TX), (unsigned)((g.ny + VE_TY - 1) / VE_TY)); }
 
 int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh) {
-    k_downhill<<<ve_tile_grid(ctx->g), VE_TX * VE_TY, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
+    k_downhill<<<ve_tile_grid(ctx->g), VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
 
 // ---------------------------------------------------------------------------------------------
 // E3b/E3c: receiver mask, donor count and MFD weights.  erosion.rs:2407-2439, 2444-2479.
-__global__ void __launch_bounds__(VE_TX * VE_TY) k_mrec(Geom g, const double* __restrict__ wh, uint8_t* __restrict__ mrec,
+__global__ void __launch_bounds__(VE_TX * VE_TR) k_mrec(Geom g, const double* __restrict__ wh, uint8_t* __restrict__ mrec,
                                                         uint8_t* __restrict__ ndon, double* __restrict__ mwrec) {
     __shared__ double s[VE_TY + 2][VE_TX + 2];
     stage_tile(g, wh, __longlong_as_double(0x7ff8000000000000LL), s);
-    const int lx = (int)(threadIdx.x % VE_TX), ly = (int)(threadIdx.x / VE_TX);
-    const int x = (int)blockIdx.x * VE_TX + lx, y = (int)blockIdx.y * VE_TY + ly;
-    if (x >= g.nx || y >= g.ny) return;
-    const uint32_t ij = g.idx(x, y);
+    const int lx = (int)(threadIdx.x % VE_TX);
+    const int x = (int)blockIdx.x * VE_TX + lx;
+    if (x >= g.nx) return;
     const double SQ = vm_sqrt(32.0 * 32.0 + 32.0 * 32.0);
-    double wh_ij = s[ly + 1][lx + 1];
-    unsigned mr = 0, nd = 0;
-    double wrec[8];
-    double sumweight = 0.0; int nrec = 0;
+    for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
+        const int y = (int)blockIdx.y * VE_TY + ly;
+        if (y >= g.ny) break;
+        const uint32_t ij = g.idx(x, y);
+        double wh_ij = s[ly + 1][lx + 1];
+        unsigned mr = 0, nd = 0;
+        double wrec[8];
+        double sumweight = 0.0; int nrec = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        wrec[k] = 0.0;
-        double wh_ijk = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];      // NaN outside the map: neither branch is taken
-        if (wh_ij > wh_ijk) {
-            mr |= 1u << k;
-            double lrec = (c_ndx[k] != 0 && c_ndy[k] != 0) ? SQ : 32.0;
-            double w = (wh_ij - wh_ijk) / lrec;
-            wrec[k] = w; sumweight += w; nrec += 1;
-        } else if (wh_ijk > wh_ij) nd += 1;
-    }
-    mrec[ij] = (uint8_t)mr; ndon[ij] = (uint8_t)nd;
-    double slope = sumweight / fmax((double)nrec, 1.0);
-    double p_mfd_exp = 0.5 + 0.6 * slope;
-    sumweight = 0.0;
+        for (int k = 0; k < 8; ++k) {
+            wrec[k] = 0.0;
+            double wh_ijk = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];      // NaN outside the map: neither branch is taken
+            if (wh_ij > wh_ijk) {
+                mr |= 1u << k;
+                double lrec = (c_ndx[k] != 0 && c_ndy[k] != 0) ? SQ : 32.0;
+                double w = (wh_ij - wh_ijk) / lrec;
+                wrec[k] = w; sumweight += w; nrec += 1;
+            } else if (wh_ijk > wh_ij) nd += 1;
+        }
+        mrec[ij] = (uint8_t)mr; ndon[ij] = (uint8_t)nd;
+        double slope = sumweight / fmax((double)nrec, 1.0);
+        double p_mfd_exp = 0.5 + 0.6 * slope;
+        sumweight = 0.0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        double w = vm_pow(wrec[k], p_mfd_exp);
-        sumweight += w; wrec[k] = w;
-    }
-    if (sumweight > 0.0) {
+        for (int k = 0; k < 8; ++k) {
+            double w = vm_pow(wrec[k], p_mfd_exp);
+            sumweight += w; wrec[k] = w;
+        }
+        if (sumweight > 0.0) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) wrec[k] /= sumweight;
+            for (int k = 0; k < 8; ++k) wrec[k] /= sumweight;
+        }
+        double2* out = reinterpret_cast<double2*>(mwrec + (size_t)ij * 8);
+        out[0] = make_double2(wrec[0], wrec[1]); out[1] = make_double2(wrec[2], wrec[3]);
+        out[2] = make_double2(wrec[4], wrec[5]); out[3] = make_double2(wrec[6], wrec[7]);
     }
-    double2* out = reinterpret_cast<double2*>(mwrec + (size_t)ij * 8);
-    out[0] = make_double2(wrec[0], wrec[1]); out[1] = make_double2(wrec[2], wrec[3]);
-    out[2] = make_double2(wrec[4], wrec[5]); out[3] = make_double2(wrec[6], wrec[7]);
 }
 
 int ve_k_mrec(ve_ctx* ctx) {
-    k_mrec<<<ve_tile_grid(ctx->g), VE_TX * VE_TY, 0, ctx->stream>>>(ctx->g, ctx->wh, ctx->mrec, ctx->ndon, ctx->mwrec);
+    k_mrec<<<ve_tile_grid(ctx->g), VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, ctx->wh, ctx->mrec, ctx->ndon, ctx->mwrec);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
@@ -234,6 +244,9 @@ int ve_k_max_slope(ve_ctx* ctx) {
 
 // ---------------------------------------------------------------------------------------------
 // E6: stream-power factors, fused pair.  erosion.rs:870-1006.
+// (ncu, round 2: with vm_pow inlined at every call site the kernel stalled on instruction fetch - `no_instruction`
+// was its top stall reason - so the receiver loop calls one out-of-line copy)
+__device__ __noinline__ double pow_ool(double x, double y) { return vm_pow(x, y); }
 __global__ void __launch_bounds__(256) k_kfactors(Geom g, ve_params P, float max_uplift, const int32_t* __restrict__ dh,
                                                   const double* __restrict__ b, const double* __restrict__ h_t,
                                                   const float* __restrict__ nf, const float* __restrict__ mf,
@@ -263,21 +276,21 @@ __global__ void __launch_bounds__(256) k_kfactors(Geom g, ve_params P, float max
         double g_i = (sed > sediment_thickness) ? (double)(1.0f * gfi) : (double)gfi;
         double r0 = ms / P.mid_slope;
         double k_da = P.k_da * (r0 * r0);
-        double ms_pow = vm_pow(ms, q_);
+        double ms_pow = pow_ool(ms, q_);
         unsigned mr = mrec[posi];
         const double* w = mwrec + (size_t)posi * 8;
         // the neighbour distance takes two values: its powers are evaluated once per cell, not once per receiver
         // (same arguments, same function: same bits)
-        const double nd_n_s = vm_pow(32.0, n), nd_n_d = vm_pow(SQ, n), nd_q_s = vm_pow(32.0, q_), nd_q_d = vm_pow(SQ, q_);
+        const double nd_n_s = pow_ool(32.0, n), nd_n_d = pow_ool(SQ, n), nd_q_s = pow_ool(32.0, q_), nd_q_d = pow_ool(SQ, q_);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
             if (!((mr >> kk) & 1u)) continue;
             double wk = w[kk];
             const bool diag = (c_ndx[kk] != 0 && c_ndy[kk] != 0);
-            double knew = kk_ * vm_pow(p * chunk_area * (area_i * wk), m) / (diag ? nd_n_d : nd_n_s);
+            double knew = kk_ * pow_ool(p * chunk_area * (area_i * wk), m) / (diag ? nd_n_d : nd_n_s);
             fs[kk] = (float)knew;
-            double k = (wk * (uplift_i + (double)max_uplift * g_i / p)) / (1.0 + k_da * vm_pow(wk * 0.1e6, q)) / ms_pow;
-            double knew2 = k * (1.0 + k_da * P.chunk_area_pow_q * vm_pow(area_i * wk, q)) / (diag ? nd_q_d : nd_q_s);
+            double k = (wk * (uplift_i + (double)max_uplift * g_i / p)) / (1.0 + k_da * pow_ool(wk * 0.1e6, q)) / ms_pow;
+            double knew2 = k * (1.0 + k_da * P.chunk_area_pow_q * pow_ool(area_i * wk, q)) / (diag ? nd_q_d : nd_q_s);
             df[kk] = (float)knew2;
         }
     }
