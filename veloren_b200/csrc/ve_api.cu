@@ -58,12 +58,10 @@ uint64_t ve_spin_limit_ns(const ve_ctx* ctx) {
 }
 
 int ve_check_abort(ve_ctx* ctx) {
-    uint32_t aw[2] = {0, 0};
-    VE_CUDA(cudaMemcpyAsync(aw, ctx->abort_word, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t a = 0;
+    VE_CUDA(cudaMemcpyAsync(&a, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
     VE_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->df_pending = 0;
-    const uint32_t a = aw[0];
-    if (aw[1]) { ctx->chains_up_ok = 0; cudaMemsetAsync(ctx->abort_word + 1, 0, 4, ctx->stream); }   // a chain field overflowed: strided order
     if (a) {
         cudaMemsetAsync(ctx->abort_word, 0, 4, ctx->stream);
         ctx->err = "dataflow sweep stalled: order is not topological (stack/newh incomplete); the context's step state is undefined, "
@@ -173,8 +171,6 @@ static int create_impl(ve_ctx* ctx, uint32_t x_lg, uint32_t y_lg, const int* dev
     VE_TRY(dev_alloc(ctx, &ctx->kfs, n * 8)); VE_TRY(dev_alloc(ctx, &ctx->kdf, n * 8));
     VE_TRY(dev_alloc(ctx, &ctx->sill_cur, n)); VE_TRY(dev_alloc(ctx, &ctx->sill_prev, n));
     VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->order_bu, n)); VE_TRY(dev_alloc(ctx, &ctx->level, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->don_live, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
-    VE_TRY(dev_alloc(ctx, &ctx->chain_word, n)); VE_TRY(dev_alloc(ctx, &ctx->chain_ext, n)); VE_TRY(dev_alloc(ctx, &ctx->corder_up, n));
-    VE_TRY(dev_alloc(ctx, &ctx->cstart_up, n + 2)); VE_TRY(dev_alloc(ctx, &ctx->chain_cnt, 64));
     VE_TRY(dev_alloc(ctx, &ctx->f_parent, n)); VE_TRY(dev_alloc(ctx, &ctx->f_jump, n)); VE_TRY(dev_alloc(ctx, &ctx->f_depth, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_root, n));
     VE_TRY(dev_alloc(ctx, &ctx->abort_word, 64));
@@ -200,7 +196,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->chains_up_ok = 0; ctx->dbg_chain_len = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
     ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
@@ -219,7 +215,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->mrec, ctx->ndon, ctx->mwrec, ctx->area, ctx->max_slope, ctx->kd_eff, ctx->h_t, ctx->h_new,
                     ctx->deltah, ctx->elev, ctx->h_p, ctx->lake_silt, ctx->lwv, ctx->wh_prev, ctx->h_spl, ctx->b_spl,
                     ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td, ctx->order_bu, ctx->level,
-                    ctx->don_order, ctx->don_live, ctx->flags, ctx->chain_word, ctx->chain_ext, ctx->corder_up, ctx->cstart_up, ctx->chain_cnt, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
+                    ctx->don_order, ctx->don_live, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -273,7 +269,6 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "thermal_sweep") ctx->dbg_thermal_sweep = (int)value;
     else if (k == "lakes_trace") ctx->dbg_lakes_trace = (int)value;
     else if (k == "lakes_serial") ctx->dbg_lakes_serial = (int)value;
-    else if (k == "chain_len") ctx->dbg_chain_len = (int)value;
     else if (k == "serial_err") ctx->dbg_serial_err = (int)value;
     else if (k == "poll_sleep_ns") ctx->dbg_poll_sleep_ns = (int)value;
     else if (k == "spin_limit_ms") ctx->spin_limit_ns = (uint64_t)(value < 0 ? 0 : value) * 1000000ull;

@@ -89,11 +89,6 @@ struct ve_ctx {
     uint32_t *order_bu;       // nodes sorted by level (longest path to a sink): sinks first
     uint32_t *don_order;      // packed donor slots sorted by stack position
     uint32_t *don_live;       // the same without egress donors (dh < 0), for the sediment sweep
-    // chained sweep orders (ve_graph.cu "chains"): per-node chain word, extension claims, nodes laid out chain by
-    // chain, chain start offsets (+ end sentinel), number of chains (device); up = dependencies are receivers
-    uint64_t *chain_word; uint32_t *chain_ext, *corder_up, *cstart_up, *chain_cnt;
-    int chains_up_ok;         // the up chains of this step are usable (no field overflowed)
-    int dbg_chain_len;        // longest chain of the chained sweep orders (<= 1: strided level order, the default)
     uint32_t *flags;          // dataflow completion epochs
     uint32_t epoch;
     uint32_t* abort_word;     // device word raised by a stalled dataflow sweep
