@@ -50,15 +50,34 @@ def test_special_values():
     assert po.vm(4, 0.0) == 0.0 and po.vm(4, 50.0) == 1.0 and po.vm(4, -50.0) == -1.0
 
 
-@pytest.mark.parametrize("lg", [5])
-def test_oracle_libm_vs_exact_math_one_step(lg):
-    """Sensitivity of a whole erode() step to the libm substitution.  A last-place difference in an
-    f64 pow can flip the f32 rounding of a k_fs/k_df factor (erosion.rs:905, 998), i.e. a 6e-8
-    relative change of one coefficient; the resulting height change stays around 1e-9."""
+def _rel(a, b):
+    s_ = np.maximum(np.abs(a), np.abs(b))
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.where(s_ > 0, np.abs(a - b) / s_, 0.0)
+
+
+def test_oracle_libm_vs_exact_math_one_step():
+    """Sensitivity of one erode() step (128x128, from identical state) to the two substitutions, each alone, in pure
+    relative terms (profiles/r02_libm_drift_*.json has the same over the full 100-step schedule):
+      * f64 pow/exp/ln/ln_1p/tanh from glibc instead of ve_exact_math.h: heights agree to ~1e-13, far inside
+        north_star's 1e-9, and every integer array is identical;
+      * the Newton loop's f32 powf(dh, 0.5) from glibc's powf instead of sqrtf: up to ~1e-5 in single cells (the
+        loop stops at tolp = 1e-3, so a last-place change of a term can change the iteration count).  The oracle
+        and the kernels use sqrtf: q_ is the constant 1.5 (erosion.rs:749), so the exponent is the literal 0.5 and
+        LLVM's libcall simplifier rewrites llvm.pow(x, 0.5) to sqrt(x) (with fabs / -inf handling) without
+        fast-math flags."""
     from veloren_b200 import synth
-    f = synth.generate(lg, lg)
-    a, b = po.Oracle(f, use_libm=False), po.Oracle(f, use_libm=True)
-    a.step(); b.step()
-    ha, hb = a.get("h"), b.get("h")
-    assert np.array_equal(a.get("dh"), b.get("dh")) and np.array_equal(a.get("mstack"), b.get("mstack"))
-    assert np.max(np.abs(ha - hb) / np.maximum(1.0, np.abs(ha))) < 1e-7
+    f = synth.generate(7, 7)
+    base = po.Oracle(f)
+    f64 = po.Oracle(f, use_libm=True, libm_f32_powf=False)
+    f32 = po.Oracle(f, use_libm=False, libm_f32_powf=True)
+    for o in (base, f64, f32):
+        o.step()
+    hb = base.get("h")
+    for name in ("dh", "indirection", "newh", "mstack", "mrec"):
+        assert np.array_equal(base.get(name), f64.get(name)), name
+    assert int(base.scalar("n_gs")) == int(f64.scalar("n_gs"))
+    r64 = _rel(hb, f64.get("h"))
+    assert r64.max() < 1e-11, r64.max()
+    r32 = _rel(hb, f32.get("h"))
+    assert r32.max() < 1e-4, r32.max()

@@ -210,9 +210,16 @@ def test_world_file_codec_round_trip(tmp_path):
     assert np.array_equal(m["alt"], alt) and np.array_equal(m["basement"], bas)
     # a 0.5.0 file: variant 0, no size header
     p2 = tmp_path / "old.bin"
-    p2.write_bytes(struct.pack("<IQ", 0, 2) + np.array([1.0, 2.0]).tobytes() + struct.pack("<Q", 2) + np.array([0.5, 1.5]).tobytes())
+    a16 = np.arange(16, dtype=np.float64)
+    p2.write_bytes(struct.pack("<IQ", 0, 16) + a16.tobytes() + struct.pack("<Q", 16) + (a16 - 0.5).tobytes())
     m2 = worldfile.load(p2)
-    assert m2["version"] == "0.5.0" and np.array_equal(m2["basement"], [0.5, 1.5])
+    assert m2["version"] == "0.5.0" and np.array_equal(m2["basement"], a16 - 0.5)
+    # WorldMap_0_5_0::into_modern: pow_size = trailing_zeros(16) / 2 = 2, scale = 2^(2 - 10)
+    assert (m2["x_lg"], m2["y_lg"]) == (2, 2) and m2["continent_scale_hack"] == 2.0 ** -8
+    p3 = tmp_path / "bad.bin"          # 8 entries is not 4^k: WorldSizeInvalid
+    p3.write_bytes(struct.pack("<IQ", 0, 8) + a16[:8].tobytes() + struct.pack("<Q", 8) + a16[:8].tobytes())
+    with pytest.raises(ValueError):
+        worldfile.load(p3)
 
 
 def test_uniform_noise_restated():

@@ -29,8 +29,10 @@ def save(path, alt, basement, x_lg, y_lg, continent_scale_hack=2.0):
 
 
 def load(path):
-    """-> dict(version, x_lg, y_lg, continent_scale_hack, alt, basement); 0.5.0 files have no size
-    (the reference assumes 1024x1024 for them, mod.rs:553-580)."""
+    """-> dict(version, x_lg, y_lg, continent_scale_hack, alt, basement).  0.5.0 files carry no size: as in
+    WorldMap_0_5_0::into_modern (mod.rs:616-635) the side is derived from the length, pow_size =
+    trailing_zeros(len) / 2 (the length must be 4^pow_size), and continent_scale_hack = 2^(pow_size - 10).
+    Inconsistent lengths raise, like WorldFileError::WorldSizeInvalid (mod.rs:619-621, 641-646)."""
     buf = open(path, "rb").read()
     (variant,) = struct.unpack_from("<I", buf, 0)
     off = 4
@@ -39,7 +41,7 @@ def load(path):
         x_lg, y_lg, scale = struct.unpack_from("<IId", buf, off); off += 16
         out.update(x_lg=x_lg, y_lg=y_lg, continent_scale_hack=scale)
     elif variant == 0:
-        out.update(x_lg=10, y_lg=10, continent_scale_hack=2.0)
+        pass                                  # size derived from the array length below
     else:
         raise ValueError("unknown WorldFile variant %d" % variant)
     arrays = []
@@ -49,4 +51,12 @@ def load(path):
     if off != len(buf):
         raise ValueError("trailing bytes in world file")
     out["alt"], out["basement"] = arrays
+    n = arrays[0].size
+    if variant == 0:
+        pow_size = ((n & -n).bit_length() - 1) // 2 if n else 0
+        if n != 1 << (2 * pow_size):
+            raise ValueError("world size of map is invalid: %d is not 4^k" % n)
+        out.update(x_lg=pow_size, y_lg=pow_size, continent_scale_hack=2.0 ** (pow_size - 10))
+    if arrays[1].size != n or n != 1 << (out["x_lg"] + out["y_lg"]) or not out["continent_scale_hack"] > 0.0:
+        raise ValueError("world size of map is invalid")
     return out
