@@ -75,6 +75,7 @@ struct ve_ctx {
     uint32_t lanes_down, lanes_up, lanes_other;   // active lanes per warp in the sweeps
     // test / tuning knobs (ve_set_debug); all zero by default
     int dbg_df_bps;           // resident blocks per SM for the sweeps (0: occupancy)
+    int bps_up, bps_down;     // resident blocks per SM of the two Gauss-Seidel sweeps (0: occupancy)
     int dbg_newton;           // bit 0: skip the Newton loop, bit 2: force the slow re-solve of every node
     int dbg_lwv_small_log;    // replay the lake_water_volume log before every Gauss-Seidel iteration
     int dbg_thermal_sweep;    // ordered sweep instead of pointer jumping for the thermal water level
