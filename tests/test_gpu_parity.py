@@ -64,11 +64,11 @@ def test_c1_256_ten_iterations_every_intermediate():
 def test_c5_plateau_256_lake_heavy():
     f = synth.generate(8, 8, kind=1)
     o, c = po.Oracle(f), _ctx(f)
-    assert True
     for it in range(4):
         o.step(); c.step()
         assert o.scalar("n_lakes") > 100 or it > 0
         _assert_step_equal(o, c, "C5 step %d" % it)
+        assert 1 <= int(c.scalar("lake_rounds")) <= 6      # the parallel lake growth ran and found its fixed point
 
 
 def test_thread_per_node_sweeps_match_too():
@@ -88,19 +88,25 @@ def test_thread_per_node_sweeps_match_too():
         _assert_step_equal(o, c, "lanes=8 plateau step %d" % it)
 
 
-@pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1)])
+@pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1),
+                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50)])
 def test_alternative_code_paths_match(knob):
     """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with the
     plain operators if a range test ever failed: newton=4 forces the second solve for every node,
     newton_variant selects another formulation of the Newton loop; serial_err=1 sums the Gauss-Seidel error in
     the reference's serial order every iteration (normally only when it lands within rounding of the
-    tolerance); thermal_sweep=1 the ordered sweep of erosion.rs:1620 instead of pointer jumping."""
-    f = synth.generate(7, 7)
-    o, c = po.Oracle(f), _ctx(f)
-    c.set_debug(**knob)
-    for it in range(3):
-        o.step(); c.step()
-        _assert_step_equal(o, c, "%s step %d" % (knob, it))
+    tolerance); thermal_sweep=1 the ordered sweep of erosion.rs:1620 instead of pointer jumping; lakes_serial=1
+    grows the lake forest with the one-warp heap (the path degenerate inputs take) instead of the parallel
+    fixed-point formulation; the last entry changes the sweeps' occupancy and poll pacing."""
+    for kind in (0, 1):
+        f = synth.generate(7, 7, kind=kind)
+        o, c = po.Oracle(f), _ctx(f)
+        c.set_debug(**knob)
+        for it in range(3 if kind == 0 else 2):
+            o.step(); c.step()
+            _assert_step_equal(o, c, "%s kind %d step %d" % (knob, kind, it))
+        if "lakes_serial" in knob:
+            assert int(c.scalar("lake_rounds")) == 0
 
 
 def test_host_noise_callback_matches_device_tables():
