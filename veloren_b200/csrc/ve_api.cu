@@ -202,10 +202,8 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
     ctx->hist_count = 0;
     ctx->up_ev_ready = false; ctx->up_ms_total = 0.0; ctx->up_launches_total = 0;
-    // resident blocks per SM of the two Gauss-Seidel sweeps: up to 2048^2 they are bound by the dependency depth and
-    // three blocks of pollers per SM beat full occupancy by 2 % (fewer warps competing for the issue slots of the
-    // warp on the critical path); larger maps want every worker
-    if (x_lg + y_lg <= 22) { ctx->bps_up = 3; ctx->bps_down = 3; }
+    // (bps_up / bps_down = 0: full occupancy.  With lane-0 staging three blocks per SM were 2 % faster; since the
+    // staging copies are spread over the lanes the sweeps are no longer issue-bound and full occupancy wins.)
     *out = ctx;
     return create_impl(ctx, x_lg, y_lg, device_ids, n_devices);
 }
