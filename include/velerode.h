@@ -129,6 +129,20 @@ int ve_set_noise_cb(ve_ctx* ctx, ve_noise_cb cb, void* user);
 /* Uploads the inputs and initialises h = oldh as f64, b = oldb as f64, wh = 0
  * (erosion.rs:2549-2559, 2601); computes max_uplift and max_g (2617-2626). */
 int ve_set_inputs(ve_ctx* ctx, const ve_inputs* in);
+/* SURVEY 8(f) rank 3 — the parameter closures of WorldSim::generate on the device (world/src/sim/mod.rs:849-893 scale
+ * factors; 1102-1337 n_func, theta_func, old_height/alt_func, uplift_fn with its uniform_noise rank CDF, kf_func, kd_func,
+ * g_func, epsilon_0_func, alpha_func).  Replaces ve_set_inputs: the twelve input arrays are computed in place on the
+ * device from what the host samples out of its noise generators (noise-rs is not part of the tree): alt_old[posi].1
+ * (mod.rs:1078-1088), uheight = uplift_nz.get(turbed wposf).clamp(-1,1)*0.5+0.5 (1222-1228) and rock_strength =
+ * rock_strength_nz.get(wposf3).clamp(-1,1)*0.5+0.5 (1234-1240), one value per chunk.  is_ocean == NULL: get_oceans on
+ * alt_old (mod.rs:1092).  gen_scale = GenOpts.scale (grid_scale = scale / 4, mod.rs:849).  `out` (may be NULL) receives
+ * copies of the arrays (any member may be NULL) and max_erosion_per_delta_t. */
+typedef struct {
+    float* oldh; uint8_t* is_ocean; float* uplift; float* n; float* m; float* g; float* epsilon_0; float* alpha;
+    double* kf; double* kd; double* height_scale_cell; double max_erosion_per_delta_t;
+} ve_inputs_out;
+int ve_set_inputs_from_fields(ve_ctx* ctx, double gen_scale, const float* alt_old, const uint8_t* is_ocean, const double* uheight,
+                              const double* rock_strength, ve_inputs_out* out);
 /* Replace the evolving state (any pointer may be NULL to keep it). */
 int ve_set_state(ve_ctx* ctx, const double* h, const double* b, const double* wh);
 

@@ -367,3 +367,61 @@ def test_uniform_noise_and_horizon_map():
         assert bit_diff(a, b) == 0
     with pytest.raises(VeError):
         c.horizon_map(10.0, 5.0, h)
+
+
+def test_parameter_closures_on_device():
+    """ve_set_inputs_from_fields against a numpy restatement of mod.rs:849-893 and 1102-1337 (f32/f64
+    casts as in the reference; log / ln_1p / tanh / pow through the oracle's exact-math probes), then a step from the
+    device-built inputs against the oracle fed with the downloaded arrays."""
+    lg = 6
+    n = 1 << (2 * lg)
+    f = synth.generate(lg, lg)
+    rng = np.random.default_rng(5)
+    # alt_old in the generator's range with an ocean border, noise samples in [0, 1]
+    nx = 1 << lg
+    yy, xx = np.divmod(np.arange(n), nx)
+    r2 = ((xx + 0.5 - nx / 2) / (nx / 2)) ** 2 + ((yy + 0.5 - nx / 2) / (nx / 2)) ** 2
+    alt_old = (0.6 - 1.1 * r2 + 0.2 * rng.standard_normal(n)).astype(np.float32)
+    uheight = rng.random(n)
+    rock = rng.random(n)
+    scale = 2.0
+    c = ErosionContext(lg, lg)
+    got = c.set_inputs_from_fields(scale, alt_old, uheight, rock)
+    # --- restatement
+    oc = po.get_oceans(lg, lg, alt_old.astype(np.float64)).astype(bool)          # mod.rs:1092
+    assert np.array_equal(got["is_ocean"].astype(bool), oc) and oc.any() and (~oc).any()
+    gs = 1.0 / (4.0 / scale)
+    hs = po.vm(2, gs, 1.0); ts = hs
+    old_height = alt_old * np.float32(2048.0) * np.float32(hs)
+    alt = np.where(oc, old_height, (old_height.astype(np.float64) / 2048.0).astype(np.float32) - np.float32(0.5)).astype(np.float32)
+    assert bit_diff(alt, got["oldh"]) == 0
+    v = old_height.copy(); v[oc] = np.nan
+    cdf = po.uniform_noise(v)
+    mn = 1.0 / max(float(n), 2.220446049250313e-16 * 0.5); mx = min(1.0 - 1.0 / n, 1.0 - 2.220446049250313e-16 * 0.5)
+    hgt = (cdf.astype(np.float64) - 0.5 + 0.5) ** 2
+    hgt = hgt * (mx - mn) + mn
+    hgt = (hgt - mn) / (mx - mn)
+    up = np.where(oc, 0.0, hgt * (64.0 * ts)).astype(np.float32)
+    assert bit_diff(up, got["uplift"]) == 0
+    kfs = po.vm(2, gs, -2.0 * float(np.float32(0.4) * np.float32(1.0)))
+    assert bit_diff(np.where(oc, 1.0e-4, 1.0e-6) * kfs, got["kf"]) == 0
+    assert bit_diff(np.full(n, (1.0e-2 / 4.0) * (gs * gs / ts)), got["kd"]) == 0
+    assert bit_diff(np.where(po.map_edge_factor(lg, lg) == 0, np.float32(0), np.float32(1)).astype(np.float32), got["g"]) == 0
+    l2b = (3.0 ** 0.5) * 0.63661977236758134308
+    logit = lambda x: po.vm(0, x) - po.vm(3, -x)
+    us = np.array([po.vm(4, (logit(min(1 - 1e-7, max(1e-7, float(rk)))) + (logit(min(0.45, max(0.35, float(uh)))) - logit(0.4))) / l2b) * 0.5 + 0.5
+                   for rk, uh in zip(rock, uheight)])
+    eps_scale = np.float32(hs / ts); a_scale = np.float32(1.0 / hs)
+    eps_land = ((1.0 - us) * (2.078e-3 - 5.3e-5) + 5.3e-5).astype(np.float32) / np.float32(4.0) * eps_scale
+    eps = np.where(oc, np.float32(2.078e-3) / np.float32(4.0) * eps_scale, eps_land).astype(np.float32)
+    al = np.where(oc, np.float32(3.7e-2) * a_scale, (us * (4.2e-2 - 1.6e-2) + 1.6e-2).astype(np.float32) * a_scale).astype(np.float32)
+    assert bit_diff(eps, got["epsilon_0"]) == 0 and bit_diff(al, got["alpha"]) == 0
+    assert got["max_erosion_per_delta_t"] == 64.0 * ts
+    assert np.all(got["n"] == 1.0) and bit_diff(got["m"], np.full(n, np.float32(0.4), np.float32)) == 0
+    # --- the context is ready to step from these inputs: same result as an oracle given the downloaded arrays
+    c.set_params(k_d_scale=f["k_d_scale"], k_da=f["k_da"]); c.set_noise(f["noise"])
+    f2 = dict(f); f2.update({k: got[k] for k in ("oldh", "oldb", "is_ocean", "uplift", "n", "m", "g", "epsilon_0", "alpha", "kf", "kd",
+                                                  "height_scale_cell")})
+    o = po.Oracle(f2)
+    o.step(); c.step()
+    _assert_step_equal(o, c, "step from device-built inputs")

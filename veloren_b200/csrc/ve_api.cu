@@ -122,6 +122,12 @@ static int mg_share(ve_ctx* ctx, void* local) {
     ctx->mg_peers[(const void*)local] = ptrs;
     return VE_OK;
 }
+int ve_k_f32_to_f64(ve_ctx* ctx, const float* a, double* o) {
+    k_f32_to_f64<<<ve_blocks(ctx->g.n, 256), 256, 0, ctx->stream>>>(ctx->g.n, a, o);
+    VE_LAUNCH_CHECK();
+    return VE_OK;
+}
+
 extern "C" {
 
 void ve_default_params(ve_params* p) {
@@ -331,6 +337,51 @@ int ve_set_inputs(ve_ctx* ctx, const ve_inputs* in) {
     // max_uplift / max_g (erosion.rs:2617-2626): scalar reductions over the host arrays the shim already holds
     float mu = in->uplift[0], mg = in->g[0];
     for (size_t i = 1; i < n; ++i) { if (in->uplift[i] > mu) mu = in->uplift[i]; if (in->g[i] > mg) mg = in->g[i]; }
+    ctx->max_uplift = mu; ctx->max_g = mg;
+    return VE_OK;
+}
+
+int ve_set_inputs_from_fields(ve_ctx* ctx, double gen_scale, const float* alt_old, const uint8_t* is_ocean, const double* uheight,
+                              const double* rock_strength, ve_inputs_out* out) {
+    if (!ctx || !alt_old || !uheight || !rock_strength || !(gen_scale > 0.0)) return VE_ERR_INVALID;
+    VE_CUDA(cudaSetDevice(ctx->device));
+    const size_t n = ctx->g.n;
+    cudaStream_t st = ctx->stream;
+    // device staging carved from arrays that a step overwrites anyway
+    float* d_alt = (float*)ctx->elev; float* d_cdf = (float*)ctx->deltah; float* d_tmp = (float*)ctx->h_p; float* d_oldh = (float*)ctx->h_new;
+    double* d_uh = ctx->area; double* d_rock = ctx->max_slope;
+    VE_CUDA(cudaMemcpyAsync(d_alt, alt_old, n * 4, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(d_uh, uheight, n * 8, cudaMemcpyHostToDevice, st));
+    VE_CUDA(cudaMemcpyAsync(d_rock, rock_strength, n * 8, cudaMemcpyHostToDevice, st));
+    if (is_ocean) VE_CUDA(cudaMemcpyAsync(ctx->ocean, is_ocean, n, cudaMemcpyHostToDevice, st));
+    else {
+        // get_oceans(map_size_lg, |posi| alt_old[posi].1) (mod.rs:1092): flood from the border over alt_old <= 0
+        VE_TRY(ve_k_f32_to_f64(ctx, d_alt, ctx->h_t));
+        VE_TRY(ve_g_get_oceans(ctx, ctx->h_t, ctx->ocean));
+    }
+    double max_erosion = 0.0;
+    VE_TRY(ve_k_erosion_inputs(ctx, gen_scale, d_alt, ctx->ocean, d_uh, d_rock, d_cdf, d_tmp, d_oldh, &max_erosion));
+    // max_uplift / max_g (erosion.rs:2617-2626): reductions over the two f32 arrays, taken on the host
+    std::vector<float> hu(n), hg(n);
+    VE_CUDA(cudaMemcpyAsync(hu.data(), ctx->uplift, n * 4, cudaMemcpyDeviceToHost, st));
+    VE_CUDA(cudaMemcpyAsync(hg.data(), ctx->gf, n * 4, cudaMemcpyDeviceToHost, st));
+    if (out) {
+        if (out->oldh) VE_CUDA(cudaMemcpyAsync(out->oldh, d_oldh, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->is_ocean) VE_CUDA(cudaMemcpyAsync(out->is_ocean, ctx->ocean, n, cudaMemcpyDeviceToHost, st));
+        if (out->uplift) VE_CUDA(cudaMemcpyAsync(out->uplift, ctx->uplift, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->n) VE_CUDA(cudaMemcpyAsync(out->n, ctx->nf, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->m) VE_CUDA(cudaMemcpyAsync(out->m, ctx->mf, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->g) VE_CUDA(cudaMemcpyAsync(out->g, ctx->gf, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->epsilon_0) VE_CUDA(cudaMemcpyAsync(out->epsilon_0, ctx->eps0, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->alpha) VE_CUDA(cudaMemcpyAsync(out->alpha, ctx->alpha, n * 4, cudaMemcpyDeviceToHost, st));
+        if (out->kf) VE_CUDA(cudaMemcpyAsync(out->kf, ctx->kf, n * 8, cudaMemcpyDeviceToHost, st));
+        if (out->kd) VE_CUDA(cudaMemcpyAsync(out->kd, ctx->kd, n * 8, cudaMemcpyDeviceToHost, st));
+        if (out->height_scale_cell) VE_CUDA(cudaMemcpyAsync(out->height_scale_cell, ctx->hscale, n * 8, cudaMemcpyDeviceToHost, st));
+        out->max_erosion_per_delta_t = max_erosion;
+    }
+    VE_CUDA(cudaStreamSynchronize(st));
+    float mu = hu[0], mg = hg[0];
+    for (size_t i = 1; i < n; ++i) { if (hu[i] > mu) mu = hu[i]; if (hg[i] > mg) mg = hg[i]; }
     ctx->max_uplift = mu; ctx->max_g = mg;
     return VE_OK;
 }

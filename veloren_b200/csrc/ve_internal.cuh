@@ -168,6 +168,7 @@ int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out);
 int ve_check_abort(ve_ctx* ctx);
 
 // ---- stage entry points (one per translation unit) ------------------------------------------
+int ve_k_f32_to_f64(ve_ctx* ctx, const float* a, double* o);      // ve_api.cu
 // ve_stencil.cu
 int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh);
 int ve_k_mrec(ve_ctx* ctx);                 // mrec, ndon, mwrec from ctx->wh
@@ -176,6 +177,8 @@ int ve_k_kfactors(ve_ctx* ctx);
 int ve_k_basement(ve_ctx* ctx);             // scatter is implicit (grid-indexed), basement + lake silt
 int ve_k_thermal_kd(ve_ctx* ctx);
 int ve_k_diffusion(ve_ctx* ctx, double dt, double* h, double* b, const double* kd_eff);
+int ve_k_erosion_inputs(ve_ctx* ctx, double gen_scale, const float* d_alt_old, const uint8_t* d_ocean, const double* d_uheight,
+                        const double* d_rock, float* d_cdf, float* d_tmp_f32, float* d_oldh_out, double* max_erosion_out);
 // ve_graph.cu
 int ve_g_wh_fill(ve_ctx* ctx);              // erosion.rs:2383-2400 along newh
 int ve_g_stack(ve_ctx* ctx);                // exact mstack + stackpos + order_td + don_order

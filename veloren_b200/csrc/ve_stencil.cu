@@ -243,6 +243,97 @@ int ve_k_max_slope(ve_ctx* ctx) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// the parameter closures of WorldSim::generate (world/src/sim/mod.rs:849-893 scale factors,
+// 1102-1337 closures) evaluated per chunk on the device, straight into the context's input arrays.  The noise-rs
+// generators they sample are not part of the tree, so the host passes the sampled values (alt_old, uheight,
+// rock_strength); everything downstream of the samples is here.  cdf = rank CDF of old_height over the land
+// chunks (uniform_noise, util.rs:171-207; mod.rs:1118-1124).
+__global__ void __launch_bounds__(256) k_erosion_inputs(Geom g, double grid_scale, double min_epsilon, double max_epsilon, double max_erosion_per_delta_t,
+                                                        const float* __restrict__ alt_old, const uint8_t* __restrict__ ocean,
+                                                        const float* __restrict__ cdf, const double* __restrict__ uheight_a,
+                                                        const double* __restrict__ rock_a, float* __restrict__ uplift, float* __restrict__ nf,
+                                                        float* __restrict__ mf, float* __restrict__ gf, float* __restrict__ eps0,
+                                                        float* __restrict__ alpha, double* __restrict__ kf, double* __restrict__ kd,
+                                                        double* __restrict__ hscale, double* __restrict__ h, double* __restrict__ b,
+                                                        double* __restrict__ wh, float* __restrict__ oldh_out) {
+    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (posi >= g.n) return;
+    const bool oc = ocean[posi] != 0;
+    const float n = 1.0f, theta = 0.4f;                                             // n_func 1102-1107, theta_func 1146
+    const double height_scale = vm_pow(grid_scale, (double)n);                      // 871
+    const double time_scale = vm_pow(grid_scale, (double)n);                        // 873
+    const float mountain_scale = 2048.0f;                                           // CONFIG.mountain_scale
+    const float old_height = alt_old[posi] * mountain_scale * (float)height_scale;  // 1108-1110
+    const float alt = oc ? old_height : (float)((double)old_height / (double)mountain_scale) - 0.5f;   // alt_func 1331-1337
+    oldh_out[posi] = alt;
+    h[posi] = (double)alt; b[posi] = (double)alt; wh[posi] = 0.0;                   // erosion.rs:2549-2559, 2601
+    nf[posi] = n; mf[posi] = theta * n;                                             // erosion.rs:2570
+    hscale[posi] = height_scale;                                                    // erosion.rs:848-850
+    // uplift_fn 1312-1330 (uplift_uniform[posi].1 = (alt_old_no_ocean.0 - 0.5 + 0.5)^2, 1125-1133), cast at erosion.rs:2607
+    double up = 0.0;
+    if (!oc) {
+        double oheight = (double)cdf[posi] - 0.5;
+        double height = (oheight + 0.5) * (oheight + 0.5);
+        height = (height - 0.0) / (1.0 - 0.0);
+        height = height * (max_epsilon - min_epsilon) + min_epsilon;
+        height = (height - min_epsilon) / (max_epsilon - min_epsilon);              // erosion_factor 1142-1144
+        up = height * max_erosion_per_delta_t;
+    }
+    uplift[posi] = (float)up;
+    const double kf_scale = vm_pow(grid_scale, -2.0 * (double)(theta * n));         // k_fs_scale 860
+    kf[posi] = (oc ? 1.0e-4 : 1.0e-6) * kf_scale;                                   // kf_func 1147-1168
+    kd[posi] = (1.0e-2 / 4.0) * (grid_scale * grid_scale / time_scale);             // kd_func 1169-1183, k_d_scale 883
+    {   // g_func 1184-1200 with map_edge_factor (util.rs:22-29)
+        int ex = g.x_of(posi), ey = g.y_of(posi);
+        float fx = (float)(g.nx / 2 - abs(ex - g.nx / 2)) / ((16.0f / 1024.0f) * (float)g.nx);
+        float fy = (float)(g.ny / 2 - abs(ey - g.ny / 2)) / ((16.0f / 1024.0f) * (float)g.ny);
+        gf[posi] = fminf(fmaxf(fminf(fx, fy), 0.0f), 1.0f) == 0.0f ? 0.0f : 1.0f;
+    }
+    const float eps_scale = (float)(height_scale / time_scale);                     // epsilon_0_scale 885
+    const float alpha_scale = (float)(1.0 / height_scale);                          // alpha_scale 879
+    if (oc) {
+        eps0[posi] = (2.078e-3f / 4.0f) * eps_scale;                                // 1206-1209
+        alpha[posi] = 3.7e-2f * alpha_scale;                                        // 1260-1262
+    } else {
+        // ustrength 1241-1249 / 1293-1301: logistic_cdf(logit(rock_strength) + logit(uheight) - logit(center))
+        const double logistic_2_base = vm_sqrt(3.0) * 0.63661977236758134308;
+        const double center = 0.4, dmin = center - 0.05, dmax = center + 0.05;
+        const double rs = fmin(1.0 - 1e-7, fmax(1e-7, rock_a[posi]));
+        const double uh = fmin(dmax, fmax(dmin, uheight_a[posi]));
+        const double arg = 1.0 * (vm_log(rs) - vm_log1p(-rs)) + 1.0 * ((vm_log(uh) - vm_log1p(-uh)) - (vm_log(center) - vm_log1p(-center)));
+        const double us = vm_tanh(arg / logistic_2_base) * 0.5 + 0.5;
+        eps0[posi] = (float)((1.0 - us) * (2.078e-3 - 5.3e-5) + 5.3e-5) / 4.0f * eps_scale;   // 1255-1256
+        alpha[posi] = (float)(us * (4.2e-2 - 1.6e-2) + 1.6e-2) * alpha_scale;                  // 1309-1310
+    }
+}
+__global__ void __launch_bounds__(256) k_land_height(uint32_t n, const float* __restrict__ alt_old, const uint8_t* __restrict__ ocean,
+                                                     float height_scale_f, float* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = ocean[i] ? __int_as_float(0x7fc00000) : alt_old[i] * 2048.0f * height_scale_f;   // None on ocean chunks (1118-1124)
+}
+int ve_k_erosion_inputs(ve_ctx* ctx, double gen_scale, const float* d_alt_old, const uint8_t* d_ocean, const double* d_uheight,
+                        const double* d_rock, float* d_cdf, float* d_tmp_f32, float* d_oldh_out, double* max_erosion_out) {
+    const Geom& g = ctx->g;
+    const uint32_t n = g.n;
+    const unsigned nb = ve_blocks(n, 256);
+    const double grid_scale = 1.0 / (4.0 / gen_scale);                                          // 849
+    const double len_f = (double)n;
+    const double min_epsilon = 1.0 / fmax(len_f, 2.220446049250313e-16 * 0.5);                  // 903
+    const double max_epsilon = fmin(1.0 - 1.0 / len_f, 1.0 - 2.220446049250313e-16 * 0.5);      // 904
+    const double max_erosion_per_delta_t = 64.0 * vm_pow(grid_scale, 1.0);                      // 889-890 (n_approx = 1)
+    k_land_height<<<nb, 256, 0, ctx->stream>>>(n, d_alt_old, d_ocean, (float)vm_pow(grid_scale, 1.0), d_tmp_f32);
+    VE_LAUNCH_CHECK();
+    VE_TRY(ve_g_uniform_noise(ctx, d_tmp_f32, d_cdf, nullptr));
+    k_erosion_inputs<<<nb, 256, 0, ctx->stream>>>(g, grid_scale, min_epsilon, max_epsilon, max_erosion_per_delta_t, d_alt_old, d_ocean, d_cdf,
+                                                  d_uheight, d_rock, ctx->uplift, ctx->nf, ctx->mf, ctx->gf, ctx->eps0, ctx->alpha, ctx->kf,
+                                                  ctx->kd, ctx->hscale, ctx->h, ctx->b, ctx->wh, d_oldh_out);
+    VE_LAUNCH_CHECK();
+    if (max_erosion_out) *max_erosion_out = max_erosion_per_delta_t;
+    return VE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // E6: stream-power factors, fused pair.  erosion.rs:870-1006.
 // (ncu, round 2: with vm_pow inlined at every call site the kernel stalled on instruction fetch - `no_instruction`
 // was its top stall reason - so the receiver loop calls one out-of-line copy)

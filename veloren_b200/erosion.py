@@ -26,7 +26,7 @@ SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_
            "up_launches_total", "lake_rounds"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
-           "ve_set_noise_cb", "ve_mg_attach", "ve_set_debug", "ve_set_inputs", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
+           "ve_set_noise_cb", "ve_mg_attach", "ve_set_debug", "ve_set_inputs", "ve_set_inputs_from_fields", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
            "ve_get_scalar", "ve_launch_count", "ve_get_history", "ve_set_timing", "ve_get_timers", "ve_timer_name", "ve_downhill",
            "ve_get_lakes", "ve_get_multi_rec", "ve_get_multi_drainage", "ve_fill_sinks", "ve_get_drainage",
            "ve_diffusion", "ve_diffusion_static", "ve_get_oceans", "ve_water_alt", "ve_get_rivers", "ve_uniform_noise",
@@ -47,6 +47,11 @@ class Params(ctypes.Structure):
 class Inputs(ctypes.Structure):
     _fields_ = [(k, ctypes.c_void_p) for k in ("oldh", "oldb", "is_ocean", "uplift", "n", "m", "g", "epsilon_0",
                                                "alpha", "kf", "kd", "height_scale_cell")]
+
+
+class InputsOut(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_void_p) for k in ("oldh", "is_ocean", "uplift", "n", "m", "g", "epsilon_0", "alpha", "kf", "kd",
+                                               "height_scale_cell")] + [("max_erosion_per_delta_t", ctypes.c_double)]
 
 
 class Noise(ctypes.Structure):
@@ -196,6 +201,24 @@ class ErosionContext:
                 raise ValueError("%s has %d entries, expected %d" % (k, a.size, self.n))
         inp = Inputs(*[_p(arrs[k]) for k, _ in Inputs._fields_])
         self._chk(lib().ve_set_inputs(self.ctx, ctypes.byref(inp)))
+
+    def set_inputs_from_fields(self, gen_scale, alt_old, uheight, rock_strength, is_ocean=None):
+        """ve_set_inputs_from_fields: the parameter closures of WorldSim::generate (mod.rs:1102-1337) evaluated on the
+        device from the host's noise samples; returns the twelve input arrays (as ve_set_inputs would take them) plus
+        max_erosion_per_delta_t, for inspection."""
+        n = self.n
+        spec = dict(oldh=np.float32, is_ocean=np.uint8, uplift=np.float32, n=np.float32, m=np.float32, g=np.float32,
+                    epsilon_0=np.float32, alpha=np.float32, kf=np.float64, kd=np.float64, height_scale_cell=np.float64)
+        arrs = {k: np.empty(n, dt) for k, dt in spec.items()}
+        out = InputsOut(*[_p(arrs[k]) for k, _ in InputsOut._fields_[:-1]], 0.0)
+        a = np.ascontiguousarray(alt_old, np.float32); u = np.ascontiguousarray(uheight, np.float64)
+        r = np.ascontiguousarray(rock_strength, np.float64)
+        oc = np.ascontiguousarray(is_ocean, np.uint8) if is_ocean is not None else None
+        self._chk(lib().ve_set_inputs_from_fields(self.ctx, ctypes.c_double(gen_scale), _p(a), _p(oc) if oc is not None else None,
+                                                  _p(u), _p(r), ctypes.byref(out)))
+        arrs["oldb"] = arrs["oldh"].copy()
+        arrs["max_erosion_per_delta_t"] = out.max_erosion_per_delta_t
+        return arrs
 
     def configure(self, fields):
         """fields: the dict veloren_b200.synth.generate returns (arrays + scalars + noise)."""
