@@ -89,7 +89,7 @@ def test_thread_per_node_sweeps_match_too():
 
 
 @pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1),
-                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1)])
+                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1), dict(rank_jump=1)])
 def test_alternative_code_paths_match(knob):
     """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with the
     plain operators if a range test ever failed: newton=4 forces the second solve for every node,

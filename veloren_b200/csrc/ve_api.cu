@@ -202,7 +202,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->dbg_rank_jump = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
     ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
@@ -277,6 +277,7 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "thermal_sweep") ctx->dbg_thermal_sweep = (int)value;
     else if (k == "lakes_trace") ctx->dbg_lakes_trace = (int)value;
     else if (k == "lakes_serial") ctx->dbg_lakes_serial = (int)value;
+    else if (k == "rank_jump") ctx->dbg_rank_jump = (int)value;
     else if (k == "level_order") ctx->dbg_level_order = (int)value;
     else if (k == "bps_up") ctx->bps_up = (int)value;
     else if (k == "bps_down") ctx->bps_down = (int)value;

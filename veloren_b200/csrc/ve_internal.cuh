@@ -91,6 +91,7 @@ struct ve_ctx {
     uint32_t *don_order;      // packed donor slots sorted by stack position
     uint32_t *don_live;       // the same without egress donors (dh < 0), for the sediment sweep
     int dbg_level_order;      // 1: the bottom-up level sweep always walks the wh-sorted stack (the path taken with tie edges)
+    int dbg_rank_jump;        // 1: list ranking always by pointer jumping over all arcs
     uint32_t *flags;          // dataflow completion epochs
     uint32_t epoch;
     uint32_t* abort_word;     // device word raised by a stalled dataflow sweep
