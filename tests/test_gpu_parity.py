@@ -89,7 +89,7 @@ def test_thread_per_node_sweeps_match_too():
 
 
 @pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1),
-                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1), dict(rank_jump=1)])
+                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1), dict(rank_jump=1), dict(quad=1)])
 def test_alternative_code_paths_match(knob):
     """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with the
     plain operators if a range test ever failed: newton=4 forces the second solve for every node,
@@ -97,7 +97,8 @@ def test_alternative_code_paths_match(knob):
     the reference's serial order every iteration (normally only when it lands within rounding of the
     tolerance); thermal_sweep=1 the ordered sweep of erosion.rs:1620 instead of pointer jumping; lakes_serial=1
     grows the lake forest with the one-warp heap (the path degenerate inputs take) instead of the parallel
-    fixed-point formulation; the last entry changes the sweeps' occupancy and poll pacing."""
+    fixed-point formulation; bps_*/poll_sleep_ns change the sweeps' occupancy and poll pacing; quad=1 runs the
+    sediment sweep with four nodes per warp over the level order padded to quads (the default from 2048^2 on)."""
     for kind in (0, 1):
         f = synth.generate(7, 7, kind=kind)
         o, c = po.Oracle(f), _ctx(f)
@@ -150,10 +151,12 @@ def test_lake_water_volume_replay_mid_loop():
         _assert_step_equal(o, c, "small lwv log step %d" % it)
 
 
-def test_non_square_and_small_maps():
+@pytest.mark.parametrize("quad", [0, 1])
+def test_non_square_and_small_maps(quad):
     for x_lg, y_lg in ((5, 7), (7, 5), (3, 3), (2, 2)):
         f = synth.generate(x_lg, y_lg)
         o, c = po.Oracle(f), _ctx(f)
+        c.set_debug(quad=quad)
         for it in range(2):
             o.step(); c.step()
             _assert_step_equal(o, c, "%dx%d step %d" % (1 << x_lg, 1 << y_lg, it))

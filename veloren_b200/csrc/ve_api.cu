@@ -177,6 +177,9 @@ static int create_impl(ve_ctx* ctx, uint32_t x_lg, uint32_t y_lg, const int* dev
     VE_TRY(dev_alloc(ctx, &ctx->kfs, n * 8)); VE_TRY(dev_alloc(ctx, &ctx->kdf, n * 8));
     VE_TRY(dev_alloc(ctx, &ctx->sill_cur, n)); VE_TRY(dev_alloc(ctx, &ctx->sill_prev, n));
     VE_TRY(dev_alloc(ctx, &ctx->order_td, n)); VE_TRY(dev_alloc(ctx, &ctx->order_bu, n)); VE_TRY(dev_alloc(ctx, &ctx->level, n)); VE_TRY(dev_alloc(ctx, &ctx->don_order, n)); VE_TRY(dev_alloc(ctx, &ctx->don_live, n)); VE_TRY(dev_alloc(ctx, &ctx->flags, n));
+    ctx->order_q_cap = (uint32_t)n + 4u * 65536u;
+    VE_TRY(dev_alloc(ctx, &ctx->order_q, (size_t)ctx->order_q_cap + 2 * (65536 + 2) + 64));
+    ctx->order_q_n = ctx->order_q + ctx->order_q_cap + 2 * (65536 + 2);
     VE_TRY(dev_alloc(ctx, &ctx->f_parent, n)); VE_TRY(dev_alloc(ctx, &ctx->f_jump, n)); VE_TRY(dev_alloc(ctx, &ctx->f_depth, n));
     VE_TRY(dev_alloc(ctx, &ctx->f_root, n));
     VE_TRY(dev_alloc(ctx, &ctx->abort_word, 64));
@@ -202,7 +205,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->dbg_rank_jump = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->order_q = nullptr; ctx->order_q_n = nullptr; ctx->order_q_cap = 0; ctx->dbg_quad = 0; ctx->dbg_rank_jump = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
     ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
@@ -223,7 +226,7 @@ void ve_destroy(ve_ctx* ctx) {
                     ctx->mrec, ctx->ndon, ctx->mwrec, ctx->area, ctx->max_slope, ctx->kd_eff, ctx->h_t, ctx->h_new,
                     ctx->deltah, ctx->elev, ctx->h_p, ctx->lake_silt, ctx->lwv, ctx->wh_prev, ctx->h_spl, ctx->b_spl,
                     ctx->wh_mrec, ctx->h_pre_diff, ctx->kfs, ctx->kdf, ctx->sill_cur, ctx->sill_prev, ctx->order_td, ctx->order_bu, ctx->level,
-                    ctx->don_order, ctx->don_live, ctx->flags, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
+                    ctx->don_order, ctx->don_live, ctx->flags, ctx->order_q, ctx->f_parent, ctx->f_jump, ctx->f_depth, ctx->f_root, ctx->abort_word,
                     ctx->d_scalars, ctx->nz.perm, ctx->cub_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
@@ -277,6 +280,7 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "thermal_sweep") ctx->dbg_thermal_sweep = (int)value;
     else if (k == "lakes_trace") ctx->dbg_lakes_trace = (int)value;
     else if (k == "lakes_serial") ctx->dbg_lakes_serial = (int)value;
+    else if (k == "quad") ctx->dbg_quad = (int)value;
     else if (k == "rank_jump") ctx->dbg_rank_jump = (int)value;
     else if (k == "level_order") ctx->dbg_level_order = (int)value;
     else if (k == "bps_up") ctx->bps_up = (int)value;

@@ -92,6 +92,9 @@ struct ve_ctx {
     uint32_t *don_live;       // the same without egress donors (dh < 0), for the sediment sweep
     int dbg_level_order;      // 1: the bottom-up level sweep always walks the wh-sorted stack (the path taken with tie edges)
     int dbg_rank_jump;        // 1: list ranking always by pointer jumping over all arcs
+    uint32_t *order_q;        // level order padded to quads (four nodes per warp in the down-sweep) + level tables
+    uint32_t order_q_cap; uint32_t *order_q_n;   // capacity in entries; padded length on the device (0: unusable)
+    int dbg_quad;             // four nodes per warp in the down-sweep: 0 = by map size, 1 = always, -1 = never
     uint32_t *flags;          // dataflow completion epochs
     uint32_t epoch;
     uint32_t* abort_word;     // device word raised by a stalled dataflow sweep
