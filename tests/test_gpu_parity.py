@@ -142,13 +142,15 @@ def test_host_noise_callback_matches_device_tables():
 
 def test_lake_water_volume_replay_mid_loop():
     """lake_water_volume updates are logged and replayed once after the Gauss-Seidel loop; a full log is
-    replayed earlier.  lwv_small_log forces a replay before every iteration (plateau: many lakes)."""
-    f = synth.generate(7, 7, kind=1)
-    o, c = po.Oracle(f), _ctx(f)
-    c.set_debug(lwv_small_log=1)
-    for it in range(3):
-        o.step(); c.step()
-        _assert_step_equal(o, c, "small lwv log step %d" % it)
+    is first compacted (adds that can no longer stand are dropped) and replayed early only if that does not make
+    room.  lwv_small_log forces either before every iteration (plateau: many lakes)."""
+    for mode in (1, 2):     # 1: replay (sort + walk) before every iteration; 2: compact the log before every iteration
+        f = synth.generate(7, 7, kind=1)
+        o, c = po.Oracle(f), _ctx(f)
+        c.set_debug(lwv_small_log=mode)
+        for it in range(3):
+            o.step(); c.step()
+            _assert_step_equal(o, c, "small lwv log (mode %d) step %d" % (mode, it))
 
 
 @pytest.mark.parametrize("quad", [0, 1])
