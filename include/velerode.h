@@ -84,7 +84,8 @@ typedef enum {
     VE_S_N_UNDERWATER,
     VE_S_UP_MS_TOTAL,        /* device milliseconds spent in up-sweep launches since ve_create (CUDA events) */
     VE_S_UP_LAUNCHES_TOTAL,  /* number of up-sweep launches since ve_create */
-    VE_S_LAKE_ROUNDS         /* fixed-point rounds of the last parallel lake growth (0: the serial path ran) */
+    VE_S_LAKE_ROUNDS,        /* fixed-point rounds of the last parallel lake growth (0: the serial path ran) */
+    VE_S_WH_UNDECIDED        /* cells the last water-surface sweep (erosion.rs:2383-2400) had to walk in order */
 } ve_scalar;
 
 void ve_default_params(ve_params* p);

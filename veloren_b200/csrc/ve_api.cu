@@ -205,7 +205,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->order_q = nullptr; ctx->order_q_n = nullptr; ctx->order_q_cap = 0; ctx->dbg_quad = 0; ctx->dbg_rank_jump = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->order_q = nullptr; ctx->order_q_n = nullptr; ctx->order_q_cap = 0; ctx->dbg_quad = 0; ctx->dbg_rank_jump = 0; ctx->dbg_wh_full_sweep = 0; ctx->n_wh_undecided = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
     ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
@@ -283,6 +283,7 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "quad") ctx->dbg_quad = (int)value;
     else if (k == "rank_jump") ctx->dbg_rank_jump = (int)value;
     else if (k == "level_order") ctx->dbg_level_order = (int)value;
+    else if (k == "wh_full_sweep") ctx->dbg_wh_full_sweep = (int)value;
     else if (k == "bps_up") ctx->bps_up = (int)value;
     else if (k == "bps_down") ctx->bps_down = (int)value;
     else if (k == "serial_err") ctx->dbg_serial_err = (int)value;
@@ -545,6 +546,7 @@ double ve_get_scalar(ve_ctx* ctx, int which) {
         case VE_S_N_LAKES: return (double)ctx->n_lakes; case VE_S_MAX_UPLIFT: return (double)ctx->max_uplift;
         case VE_S_MAX_G: return (double)ctx->max_g;   case VE_S_N_UNDERWATER: return (double)ctx->n_underwater;
         case VE_S_LAKE_ROUNDS: return (double)ctx->lake_rounds;
+        case VE_S_WH_UNDECIDED: return (double)ctx->n_wh_undecided;
         case VE_S_UP_MS_TOTAL: return ctx->up_ms_total; case VE_S_UP_LAUNCHES_TOTAL: return (double)ctx->up_launches_total;
     }
     return NAN;

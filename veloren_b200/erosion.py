@@ -23,7 +23,7 @@ _DTYPES = dict(h=np.float64, b=np.float64, wh=np.float64, dh=np.int32, indirecti
                lake_water_volume=np.float64, kd_eff=np.float64, dh0=np.int32, wh_mrec=np.float64, b_spl=np.float64,
                h_pre_diff=np.float64)
 SCALARS = ["n_gs", "err", "maxh", "boundary_len", "n_lakes", "max_uplift", "max_g", "n_underwater", "up_ms_total",
-           "up_launches_total", "lake_rounds"]
+           "up_launches_total", "lake_rounds", "wh_undecided"]
 
 EXPORTS = ["ve_default_params", "ve_create", "ve_destroy", "ve_last_error", "ve_set_params", "ve_set_noise",
            "ve_set_noise_cb", "ve_mg_attach", "ve_set_debug", "ve_set_inputs", "ve_set_inputs_from_fields", "ve_set_state", "ve_run", "ve_step", "ve_run_device", "ve_run_device_timed", "ve_get_array", "ve_array_bytes",
