@@ -58,9 +58,10 @@ uint64_t ve_spin_limit_ns(const ve_ctx* ctx) {
 }
 
 int ve_check_abort(ve_ctx* ctx) {
-    uint32_t a = 0;
-    VE_CUDA(cudaMemcpyAsync(&a, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    volatile uint32_t* ha = reinterpret_cast<volatile uint32_t*>(ctx->h_scalars + 8);    // pinned: a plain async copy
+    VE_CUDA(cudaMemcpyAsync((void*)ha, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
     VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint32_t a = *ha;
     ctx->df_pending = 0;
     if (a) {
         cudaMemsetAsync(ctx->abort_word, 0, 4, ctx->stream);
