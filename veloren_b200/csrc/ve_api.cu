@@ -57,6 +57,19 @@ uint64_t ve_spin_limit_ns(const ve_ctx* ctx) {
     return 5000000000ull + (uint64_t)ctx->g.n * 200ull;
 }
 
+int ve_d2h2(ve_ctx* ctx, void* dst0, const void* src0, size_t bytes0, void* dst1, const void* src1, size_t bytes1) {
+    // h_scalars[0..15] belong to the Gauss-Seidel loop and ve_check_abort; [16..63] (384 bytes) stage these reads
+    char* stage = reinterpret_cast<char*>(ctx->h_scalars + 16);
+    if (bytes0 > 192 || bytes1 > 192) { ctx->err = "ve_d2h: read too large for the pinned block"; return VE_ERR_INVALID; }
+    VE_CUDA(cudaMemcpyAsync(stage, src0, bytes0, cudaMemcpyDeviceToHost, ctx->stream));
+    if (bytes1) VE_CUDA(cudaMemcpyAsync(stage + 192, src1, bytes1, cudaMemcpyDeviceToHost, ctx->stream));
+    VE_CUDA(cudaStreamSynchronize(ctx->stream));
+    memcpy(dst0, stage, bytes0);
+    if (bytes1) memcpy(dst1, stage + 192, bytes1);
+    return VE_OK;
+}
+int ve_d2h(ve_ctx* ctx, void* dst, const void* src, size_t bytes) { return ve_d2h2(ctx, dst, src, bytes, nullptr, nullptr, 0); }
+
 int ve_check_abort(ve_ctx* ctx) {
     volatile uint32_t* ha = reinterpret_cast<volatile uint32_t*>(ctx->h_scalars + 8);    // pinned: a plain async copy
     VE_CUDA(cudaMemcpyAsync((void*)ha, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));

@@ -173,6 +173,9 @@ int ve_scratch(ve_ctx* ctx, int i, size_t bytes, void** out);
 int ve_cub_tmp(ve_ctx* ctx, size_t bytes, void** out);
 // synchronise and turn a raised abort word into VE_ERR_STACK_INCOMPLETE
 int ve_check_abort(ve_ctx* ctx);
+// small device-to-host reads (counts, flags) through the context's pinned block: copy, wait for the stream, hand over
+int ve_d2h(ve_ctx* ctx, void* dst, const void* src, size_t bytes);
+int ve_d2h2(ve_ctx* ctx, void* dst0, const void* src0, size_t bytes0, void* dst1, const void* src1, size_t bytes1);
 
 // ---- stage entry points (one per translation unit) ------------------------------------------
 int ve_k_f32_to_f64(ve_ctx* ctx, const float* a, double* o);      // ve_api.cu

@@ -685,8 +685,7 @@ static int lake_grow_parallel(ve_ctx* ctx, PassTable t, uint32_t cap, uint32_t n
     k_lg_edges<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, t, dh0, lrank, L, small + 16, ehb_in, idx_in, erec_in);
     VE_LAUNCH_CHECK();
     uint32_t M = 0;
-    VE_CUDA(cudaMemcpyAsync(&M, small + 16, 4, cudaMemcpyDeviceToHost, st));
-    VE_CUDA(cudaStreamSynchronize(st));
+    VE_TRY(ve_d2h(ctx, &M, small + 16, 4));
     if (M == 0 || M > n_cross) { ctx->err = "get_lakes: pass table inconsistent"; return VE_ERR_LAKE_GRAPH; }
     const unsigned mb = ve_blocks(M, 256), vbk = ve_blocks(V, 256), lb = ve_blocks(L, 256);
     size_t tmp_bytes = 0; void* tmp;
@@ -710,8 +709,7 @@ static int lake_grow_parallel(ve_ctx* ctx, PassTable t, uint32_t cap, uint32_t n
         k_lg_orient<<<mb, 256, 0, st>>>(M, erec, pos, gs, ge, obits, key_lo, round == 0 ? 1 : 0, (int*)(small + 18));
         VE_LAUNCH_CHECK();
         uint32_t hflag[4] = {0, 0, 0, 0};   // toolarge, changed, bad, sel
-        VE_CUDA(cudaMemcpyAsync(hflag, small + 17, 16, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, hflag, small + 17, 16));
         if (hflag[0]) return VE_OK;                                  // a huge equal-height group: serial path
         if (hflag[2]) { ctx->err = "get_lakes: inconsistent lake graph (parallel growth)"; return VE_ERR_LAKE_GRAPH; }
         if (round > 0 && !hflag[1]) { converged = true; break; }   // orientation repeated: the previous round's result stands
@@ -728,14 +726,12 @@ static int lake_grow_parallel(ve_ctx* ctx, PassTable t, uint32_t cap, uint32_t n
             ctx->launches++;
         }
         uint32_t sel = 0;
-        VE_CUDA(cudaMemcpyAsync(&sel, small + 20, 4, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, &sel, small + 20, 4));
         const uint32_t* comp = sel ? comp_b : comp_a;
         k_lg_check<<<vbk, 256, 0, st>>>(V, comp, (int*)(small + 21));
         VE_LAUNCH_CHECK();
         uint32_t disc = 0;
-        VE_CUDA(cudaMemcpyAsync(&disc, small + 21, 4, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, &disc, small + 21, 4));
         if (disc) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
         // rooted spanning tree: parent and parent pass of every lake
         VE_CUDA(cudaMemsetAsync(deg, 0, Vc * 4, st));
@@ -988,8 +984,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         VE_CUDA(cudaMemsetAsync(changed, 0, 4, st));
         for (int r = 0; r < 3; ++r) { k_root_jump<<<nb, 256, 0, st>>>(n, root, changed); VE_LAUNCH_CHECK(); }
         int hc = 0;
-        VE_CUDA(cudaMemcpyAsync(&hc, changed, 4, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, &hc, changed, 4));
         if (!hc) break;
     }
     VE_CUDA(cudaMemsetAsync(size, 0, (size_t)n * 4, st));
@@ -1024,8 +1019,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     k_pass_scan<<<nb, 256, 0, st>>>(g, 0, h, dh0, root, bfskey, t, small + 2);
     VE_LAUNCH_CHECK();
     uint32_t hs[16];
-    VE_CUDA(cudaMemcpyAsync(hs, small, 64, cudaMemcpyDeviceToHost, st));
-    VE_CUDA(cudaStreamSynchronize(st));
+    VE_TRY(ve_d2h(ctx, hs, small, 64));
     const uint32_t n_boundary = hs[0], n_lakes = hs[1], n_cross = hs[2];
     { unsigned long long mb; memcpy(&mb, hs + 6, 8); double mh; memcpy(&mh, &mb, 8); ctx->maxh = mh; }
     ctx->boundary_len = n_boundary; ctx->n_lakes = n_lakes;
@@ -1098,8 +1092,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         k_adj_build<<<ve_blocks(cap, 256), 256, 0, st>>>(cap, 1, t, dh0, lrank, off, deg, adj_ft, adj_tgt, adj_k0, ck0, ck1, cand_pl, small + 3);
         VE_LAUNCH_CHECK();
         uint32_t n_cand = 0;
-        VE_CUDA(cudaMemcpyAsync(&n_cand, small + 3, 4, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, &n_cand, small + 3, 4));
         // initial heap = candidates sorted by (k0, k1) (a sorted array is a valid heap): LSD, k1 first
         uint64_t *h0 = ck0, *h1 = ck1; uint4* h2 = cand_pl;
         if (n_cand > 1) {
@@ -1136,8 +1129,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
         }
         VE_LAUNCH_CHECK();
         uint32_t cstat[6] = {0, 0, 0, 0, 0, 0};
-        VE_CUDA(cudaMemcpyAsync(cstat, small + 12, 24, cudaMemcpyDeviceToHost, st));
-        VE_CUDA(cudaStreamSynchronize(st));
+        VE_TRY(ve_d2h(ctx, cstat, small + 12, 24));
         n_flows = cstat[0];
         if (pc.on) fprintf(stderr, "[lakes] lakes %u cand %u pops %u pushes %u; kcycles sift %u scan %u push %u\n", n_lakes, n_cand, cstat[1], cstat[2], cstat[3], cstat[4], cstat[5]);
         if (n_flows != n_lakes) { ctx->err = "Disconnected lake!"; return VE_ERR_DISCONNECTED_LAKE; }
@@ -1197,8 +1189,7 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     ctx->launches += 4;
     pc.mark("final order");
     int hbad = 0;
-    VE_CUDA(cudaMemcpyAsync(&hbad, bad, 4, cudaMemcpyDeviceToHost, st));
-    VE_CUDA(cudaStreamSynchronize(st));
+    VE_TRY(ve_d2h(ctx, &hbad, bad, 4));
     if (hbad) { ctx->err = "get_lakes: inconsistent lake graph"; return VE_ERR_LAKE_GRAPH; }
     return VE_OK;
 }
