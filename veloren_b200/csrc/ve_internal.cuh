@@ -210,3 +210,12 @@ int ve_g_water_alt(ve_ctx* ctx, const double* alt, const uint8_t* ocean, const i
 int ve_list_rank(ve_ctx* ctx, uint32_t n_arcs, uint32_t* succ /*in, destroyed*/, int32_t* w0, int32_t* w1);
 // ve_lakes.cu
 int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirection, uint32_t* newh);
+
+// cp.async staging (global -> shared, 4 / 8 / 16 bytes), one commit group per pipeline step
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cpa4(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cpa8(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cpa16(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cpa_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+

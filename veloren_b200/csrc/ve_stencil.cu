@@ -22,35 +22,65 @@ __device__ __forceinline__ void stage_tile(const Geom& g, const double* __restri
     }
     __syncthreads();
 }
+// k_downhill is a pure stream (13 B per cell, no arithmetic to speak of), so it is the one stencil that runs as a
+// persistent kernel: every CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ... and copies the NEXT tile into the
+// second shared buffer with cp.async while it works on the current one (a one-shot CTA per tile left the memory
+// system idle during every compute phase: 36 % of the HBM copy rate at 4096^2).
 __global__ void __launch_bounds__(VE_TX * VE_TR) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
-                                                            int use_h_le0, int32_t* __restrict__ dh) {
-    __shared__ double s[VE_TY + 2][VE_TX + 2];
-    stage_tile(g, h, INFINITY, s);
-    const int lx = (int)(threadIdx.x % VE_TX);
-    const int x = (int)blockIdx.x * VE_TX + lx;
-    if (x >= g.nx) return;
-#pragma unroll
-    for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
-        const int y = (int)blockIdx.y * VE_TY + ly;
-        if (y >= g.ny) break;
-        const uint32_t posi = g.idx(x, y);
-        double nh = s[ly + 1][lx + 1];
-        bool oc = ocean[posi] != 0;
-        if (use_h_le0) oc = oc && (nh <= 0.0);
-        int best = -1; double besth = nh;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            double nbh = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
-            if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
+                                                            int use_h_le0, int32_t* __restrict__ dh, uint32_t tiles_x, uint32_t n_tiles) {
+    __shared__ double s[2][VE_TY + 2][VE_TX + 2];
+    auto stage = [&](int buf, uint32_t tile) {
+        const int x0 = (int)(tile % tiles_x) * VE_TX - 1, y0 = (int)(tile / tiles_x) * VE_TY - 1;
+#pragma unroll 5
+        for (int i = (int)threadIdx.x; i < (VE_TX + 2) * (VE_TY + 2); i += VE_TX * VE_TR) {
+            const int ty = i / (VE_TX + 2), tx = i - ty * (VE_TX + 2);
+            const int x = x0 + tx, y = y0 + ty;
+            if (g.inb(x, y)) cpa8(&s[buf][ty][tx], h + g.idx(x, y));
+            else s[buf][ty][tx] = INFINITY;                          // never a lower neighbour
         }
-        dh[posi] = oc ? -2 : best;
+        cpa_commit();
+    };
+    uint32_t tile = blockIdx.x;
+    if (tile < n_tiles) stage(0, tile);
+    const int lx = (int)(threadIdx.x % VE_TX);
+    for (int buf = 0; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+        const uint32_t next = tile + gridDim.x;
+        if (next < n_tiles) { stage(buf ^ 1, next); cpa_wait<1>(); } else cpa_wait<0>();
+        __syncthreads();
+        const int x = (int)(tile % tiles_x) * VE_TX + lx;
+        const int ybase = (int)(tile / tiles_x) * VE_TY;
+        if (x < g.nx) {
+#pragma unroll
+            for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
+                const int y = ybase + ly;
+                if (y >= g.ny) break;
+                const uint32_t posi = g.idx(x, y);
+                double nh = s[buf][ly + 1][lx + 1];
+                bool oc = ocean[posi] != 0;
+                if (use_h_le0) oc = oc && (nh <= 0.0);
+                int best = -1; double besth = nh;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    double nbh = s[buf][ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
+                    if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
+                }
+                dh[posi] = oc ? -2 : best;
+            }
+        }
+        __syncthreads();                                             // the buffer is refilled two tiles later
     }
 }
 
 static inline dim3 ve_tile_grid(const Geom& g) { return dim3((unsigned)((g.nx + VE_TX - 1) / VE_TX), (unsigned)((g.ny + VE_TY - 1) / VE_TY)); }
 
 int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh) {
-    k_downhill<<<ve_tile_grid(ctx->g), VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
+    const dim3 tg = ve_tile_grid(ctx->g);
+    const uint32_t tiles_x = tg.x, n_tiles = tg.x * tg.y;
+    int bps = 0;
+    VE_TRY(ve_occupancy(ctx, (const void*)k_downhill, VE_TX * VE_TR, 0, &bps));
+    uint32_t grid = (uint32_t)(bps * ctx->sm_count);
+    if (grid > n_tiles) grid = n_tiles;
+    k_downhill<<<grid, VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh, tiles_x, n_tiles);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
@@ -433,17 +463,30 @@ __global__ void __launch_bounds__(256) k_basement(Geom g, float max_uplift, cons
 
 // E11: lake silt (erosion.rs:1535-1556).  lake_silt / sill are grid-indexed here; lwv keeps the
 // reference's mixed index space (slot = the stored sill value).
+// Four consecutive cells per thread: the stage is a three-level chain of dependent loads (sill -> lwv[sill] -> h, silt,
+// wh) with one cell's worth of bytes in flight per thread; four independent chains per thread keep HBM busy.
+#define VE_LS_CELLS 4
 __global__ void __launch_bounds__(256) k_lake_silt(Geom g, double* __restrict__ h, const double* __restrict__ wh,
                                                    const int32_t* __restrict__ sill, const double* __restrict__ lake_silt,
                                                    const double* __restrict__ lwv) {
-    uint32_t posi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (posi >= g.n) return;
-    int32_t lposi = sill[posi];
-    if (lposi >= 0) {
-        double vol = lwv[lposi];
-        if (vol > 0.0) {
+    const uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) * VE_LS_CELLS;
+    if (base >= g.n) return;
+    int32_t lp[VE_LS_CELLS]; double vol[VE_LS_CELLS];
+    if (base + VE_LS_CELLS <= g.n) {
+        const int4 q = *reinterpret_cast<const int4*>(sill + base);
+        lp[0] = q.x; lp[1] = q.y; lp[2] = q.z; lp[3] = q.w;
+    } else {
+#pragma unroll
+        for (int c = 0; c < VE_LS_CELLS; ++c) lp[c] = base + c < g.n ? sill[base + c] : -1;
+    }
+#pragma unroll
+    for (int c = 0; c < VE_LS_CELLS; ++c) vol[c] = lp[c] >= 0 ? lwv[lp[c]] : 0.0;
+#pragma unroll
+    for (int c = 0; c < VE_LS_CELLS; ++c) {
+        if (lp[c] >= 0 && vol[c] > 0.0) {
+            const uint32_t posi = base + c;
             double hv = h[posi];
-            hv += fmax(0.0, fmin(lake_silt[posi], vol)) / vol * (wh[posi] - hv);
+            hv += fmax(0.0, fmin(lake_silt[posi], vol[c])) / vol[c] * (wh[posi] - hv);
             h[posi] = hv;
         }
     }
@@ -456,7 +499,7 @@ int ve_k_basement(ve_ctx* ctx) {
     VE_LAUNCH_CHECK();
     VE_CUDA(cudaMemcpyAsync(ctx->b_spl, ctx->b, (size_t)ctx->g.n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
     if (ctx->max_g > 0.0f) {
-        k_lake_silt<<<nb, 256, 0, ctx->stream>>>(ctx->g, ctx->h, ctx->wh, ctx->sill_cur, ctx->lake_silt, ctx->lwv);
+        k_lake_silt<<<ve_blocks((ctx->g.n + VE_LS_CELLS - 1) / VE_LS_CELLS, 256), 256, 0, ctx->stream>>>(ctx->g, ctx->h, ctx->wh, ctx->sill_cur, ctx->lake_silt, ctx->lwv);
         VE_LAUNCH_CHECK();
     }
     return VE_OK;
