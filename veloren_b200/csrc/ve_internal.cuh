@@ -218,4 +218,5 @@ __device__ __forceinline__ void cpa8(void* s, const void* g) { asm volatile("cp.
 __device__ __forceinline__ void cpa16(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(s)), "l"(g) : "memory"); }
 __device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cpa_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
+// neighbour slot -> delta without a table lookup (lane-varying slot): slots 0..7 = the 3x3 ring in row order
+__device__ __forceinline__ void slot_delta(int k, int& dx, int& dy) { int kk = k + (k >= 4 ? 1 : 0); dy = kk / 3 - 1; dx = kk - (dy + 1) * 3 - 1; }

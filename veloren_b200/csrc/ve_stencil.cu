@@ -22,65 +22,35 @@ __device__ __forceinline__ void stage_tile(const Geom& g, const double* __restri
     }
     __syncthreads();
 }
-// k_downhill is a pure stream (13 B per cell, no arithmetic to speak of), so it is the one stencil that runs as a
-// persistent kernel: every CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ... and copies the NEXT tile into the
-// second shared buffer with cp.async while it works on the current one (a one-shot CTA per tile left the memory
-// system idle during every compute phase: 36 % of the HBM copy rate at 4096^2).
 __global__ void __launch_bounds__(VE_TX * VE_TR) k_downhill(Geom g, const double* __restrict__ h, const uint8_t* __restrict__ ocean,
-                                                            int use_h_le0, int32_t* __restrict__ dh, uint32_t tiles_x, uint32_t n_tiles) {
-    __shared__ double s[2][VE_TY + 2][VE_TX + 2];
-    auto stage = [&](int buf, uint32_t tile) {
-        const int x0 = (int)(tile % tiles_x) * VE_TX - 1, y0 = (int)(tile / tiles_x) * VE_TY - 1;
-#pragma unroll 5
-        for (int i = (int)threadIdx.x; i < (VE_TX + 2) * (VE_TY + 2); i += VE_TX * VE_TR) {
-            const int ty = i / (VE_TX + 2), tx = i - ty * (VE_TX + 2);
-            const int x = x0 + tx, y = y0 + ty;
-            if (g.inb(x, y)) cpa8(&s[buf][ty][tx], h + g.idx(x, y));
-            else s[buf][ty][tx] = INFINITY;                          // never a lower neighbour
-        }
-        cpa_commit();
-    };
-    uint32_t tile = blockIdx.x;
-    if (tile < n_tiles) stage(0, tile);
+                                                            int use_h_le0, int32_t* __restrict__ dh) {
+    __shared__ double s[VE_TY + 2][VE_TX + 2];
+    stage_tile(g, h, INFINITY, s);
     const int lx = (int)(threadIdx.x % VE_TX);
-    for (int buf = 0; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
-        const uint32_t next = tile + gridDim.x;
-        if (next < n_tiles) { stage(buf ^ 1, next); cpa_wait<1>(); } else cpa_wait<0>();
-        __syncthreads();
-        const int x = (int)(tile % tiles_x) * VE_TX + lx;
-        const int ybase = (int)(tile / tiles_x) * VE_TY;
-        if (x < g.nx) {
+    const int x = (int)blockIdx.x * VE_TX + lx;
+    if (x >= g.nx) return;
 #pragma unroll
-            for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
-                const int y = ybase + ly;
-                if (y >= g.ny) break;
-                const uint32_t posi = g.idx(x, y);
-                double nh = s[buf][ly + 1][lx + 1];
-                bool oc = ocean[posi] != 0;
-                if (use_h_le0) oc = oc && (nh <= 0.0);
-                int best = -1; double besth = nh;
+    for (int ly = (int)(threadIdx.x / VE_TX); ly < VE_TY; ly += VE_TR) {
+        const int y = (int)blockIdx.y * VE_TY + ly;
+        if (y >= g.ny) break;
+        const uint32_t posi = g.idx(x, y);
+        double nh = s[ly + 1][lx + 1];
+        bool oc = ocean[posi] != 0;
+        if (use_h_le0) oc = oc && (nh <= 0.0);
+        int best = -1; double besth = nh;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    double nbh = s[buf][ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
-                    if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
-                }
-                dh[posi] = oc ? -2 : best;
-            }
+        for (int k = 0; k < 8; ++k) {
+            double nbh = s[ly + 1 + c_ndy[k]][lx + 1 + c_ndx[k]];
+            if (nbh < besth) { besth = nbh; best = (int)g.idx(x + c_ndx[k], y + c_ndy[k]); }
         }
-        __syncthreads();                                             // the buffer is refilled two tiles later
+        dh[posi] = oc ? -2 : best;
     }
 }
 
 static inline dim3 ve_tile_grid(const Geom& g) { return dim3((unsigned)((g.nx + VE_TX - 1) / VE_TX), (unsigned)((g.ny + VE_TY - 1) / VE_TY)); }
 
 int ve_k_downhill(ve_ctx* ctx, const double* h, const uint8_t* ocean, int use_h_le0, int32_t* dh) {
-    const dim3 tg = ve_tile_grid(ctx->g);
-    const uint32_t tiles_x = tg.x, n_tiles = tg.x * tg.y;
-    int bps = 0;
-    VE_TRY(ve_occupancy(ctx, (const void*)k_downhill, VE_TX * VE_TR, 0, &bps));
-    uint32_t grid = (uint32_t)(bps * ctx->sm_count);
-    if (grid > n_tiles) grid = n_tiles;
-    k_downhill<<<grid, VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh, tiles_x, n_tiles);
+    k_downhill<<<ve_tile_grid(ctx->g), VE_TX * VE_TR, 0, ctx->stream>>>(ctx->g, h, ocean, use_h_le0, dh);
     VE_LAUNCH_CHECK();
     return VE_OK;
 }
