@@ -113,9 +113,13 @@ int ve_mg_attach(ve_ctx* ctx, int rank, int world, ve_allgather_cb cb, void* use
 /* Test and tuning knobs (no counterpart in the reference; defaults are what production uses).  Keys:
  * "lanes_up" / "lanes_down" / "lanes_other" (k > 1: thread-per-node sweeps), "df_bps" (resident blocks per SM
  * of the sweeps), "newton" (bit 0: skip the Newton loop, bit 2: force the slow re-solve), "newton_variant",
- * "lwv_small_log", "thermal_sweep", "lakes_trace", "lakes_serial" (one-warp heap growth of the lake forest),
- * "poll_sleep_ns", "serial_err" (always sum the Gauss-Seidel error in the
- * reference's serial order), "spin_limit_ms" (give-up time of a stalled sweep). */
+ * "lwv_small_log" (1: replay, 2: compact the lake_water_volume log before every iteration), "thermal_sweep",
+ * "lakes_trace", "lakes_serial" (one-warp heap growth of the lake forest), "poll_sleep_ns", "serial_err" (always
+ * sum the Gauss-Seidel error in the reference's serial order), "spin_limit_ms" (give-up time of a stalled sweep),
+ * "bps_up" / "bps_down" (resident blocks per SM of the two Gauss-Seidel sweeps), "level_order", "rank_jump",
+ * "rank_launches" (one launch per pointer-jumping round instead of one cooperative launch), "quad" (four nodes per
+ * warp in the sediment sweep: 1 always, -1 never, 0 from 2048x2048 cells on), "wh_full_sweep" (the water-surface
+ * sweep walks every cell). */
 int ve_set_debug(ve_ctx* ctx, const char* key, long long value);
 int ve_set_params(ve_ctx* ctx, const ve_params* p);
 int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz);
