@@ -71,6 +71,7 @@ int ve_d2h2(ve_ctx* ctx, void* dst0, const void* src0, size_t bytes0, void* dst1
 int ve_d2h(ve_ctx* ctx, void* dst, const void* src, size_t bytes) { return ve_d2h2(ctx, dst, src, bytes, nullptr, nullptr, 0); }
 
 int ve_check_abort(ve_ctx* ctx) {
+    if (!ctx->df_pending) return VE_OK;                  // no sweep launched since the last look: nothing can have stalled
     volatile uint32_t* ha = reinterpret_cast<volatile uint32_t*>(ctx->h_scalars + 8);    // pinned: a plain async copy
     VE_CUDA(cudaMemcpyAsync((void*)ha, ctx->abort_word, 4, cudaMemcpyDeviceToHost, ctx->stream));
     VE_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -43,6 +43,23 @@ __global__ void __launch_bounds__(256) k_root_jump(uint32_t n, uint32_t* root, i
     uint32_t rr = root[r];
     if (rr != r) { root[i] = rr; *changed = 1; }
 }
+// all rounds of the root search in one cooperative launch: in-place jumping (roots are fixed points, so a pointer read
+// mid-update is only ever further along), a grid barrier per round, stop after the first round that moved nothing
+__global__ void __launch_bounds__(256) k_root_jump_all(uint32_t n, uint32_t* root, uint32_t* flags, int max_rounds) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (int r = 0; r < max_rounds; ++r) {
+        bool moved = false;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const uint32_t a = __ldcg(root + i);
+            const uint32_t b = __ldcg(root + a);
+            if (b != a) { root[i] = b; moved = true; }
+        }
+        if (__syncthreads_or(moved) && threadIdx.x == 0) flags[r] = 1u;
+        grid.sync();
+        if (__ldcg(flags + r) == 0u) break;
+    }
+}
 __global__ void __launch_bounds__(256) k_lake_stats(uint32_t n, const int32_t* __restrict__ dh, const uint32_t* __restrict__ root,
                                                     const double* __restrict__ h, uint32_t* __restrict__ size,
                                                     unsigned long long* __restrict__ maxh_bits, uint32_t* __restrict__ counts) {
@@ -980,12 +997,24 @@ int ve_l_get_lakes(ve_ctx* ctx, const double* h, int32_t* dh, int32_t* indirecti
     // (i) roots by pointer jumping
     k_root_init<<<nb, 256, 0, st>>>(n, dh0, root);
     VE_LAUNCH_CHECK();
-    for (int round = 0; round < 64; ++round) {
-        VE_CUDA(cudaMemsetAsync(changed, 0, 4, st));
-        for (int r = 0; r < 3; ++r) { k_root_jump<<<nb, 256, 0, st>>>(n, root, changed); VE_LAUNCH_CHECK(); }
-        int hc = 0;
-        VE_TRY(ve_d2h(ctx, &hc, changed, 4));
-        if (!hc) break;
+    if (ctx->dbg_rank_launches) {
+        for (int round = 0; round < 64; ++round) {
+            VE_CUDA(cudaMemsetAsync(changed, 0, 4, st));
+            for (int r = 0; r < 3; ++r) { k_root_jump<<<nb, 256, 0, st>>>(n, root, changed); VE_LAUNCH_CHECK(); }
+            int hc = 0;
+            VE_TRY(ve_d2h(ctx, &hc, changed, 4));
+            if (!hc) break;
+        }
+    } else {
+        uint32_t* flags = small + 128;                                       // 64 round flags (cleared with `small`)
+        int max_rounds = 64, bps = 0;
+        VE_TRY(ve_occupancy(ctx, (const void*)k_root_jump_all, 256, 0, &bps));
+        unsigned grid = (unsigned)(bps * ctx->sm_count);
+        if (grid > nb) grid = nb;
+        uint32_t nn = n;
+        void* args[] = {(void*)&nn, (void*)&root, (void*)&flags, (void*)&max_rounds};
+        VE_CUDA(cudaLaunchCooperativeKernel((void*)k_root_jump_all, dim3(grid), dim3(256), args, 0, st));
+        ctx->launches++;
     }
     VE_CUDA(cudaMemsetAsync(size, 0, (size_t)n * 4, st));
     k_lake_stats<<<nb, 256, 0, st>>>(n, dh0, root, h, size, (unsigned long long*)(small + 6), small);
