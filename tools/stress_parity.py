@@ -1,5 +1,6 @@
 """Randomised parity sweep: seeds x sizes x kinds x scales, a few erode() steps each, every intermediate compared
-bit for bit with the oracle (needs a GPU).  usage: python tools/stress_parity.py [n_cases] [rng_seed]"""
+bit for bit with the oracle (needs a GPU).  usage: python tools/stress_parity.py [n_cases] [rng_seed] [knob=value ...]
+(knobs: ve_set_debug keys applied to every context, e.g. quad=1 lwv_small_log=2)"""
 import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
@@ -11,6 +12,7 @@ from oracle import pyoracle as po
 
 n_cases = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 rng = np.random.RandomState(int(sys.argv[2]) if len(sys.argv) > 2 else 12345)
+knobs = {k: int(v) for k, v in (a.split("=") for a in sys.argv[3:])}
 bad_total = 0
 t0 = time.time()
 for case in range(n_cases):
@@ -22,6 +24,8 @@ for case in range(n_cases):
     f = synth.generate(x_lg, y_lg, seed=seed, kind=kind, scale=scale)
     o = po.Oracle(f, n_threads=os.cpu_count())
     c = ErosionContext(x_lg, y_lg); c.configure(f)
+    if knobs:
+        c.set_debug(**knobs)
     status = "ok"
     for it in range(steps):
         o.step(); c.step()
