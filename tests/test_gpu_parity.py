@@ -89,7 +89,7 @@ def test_thread_per_node_sweeps_match_too():
 
 
 @pytest.mark.parametrize("knob", [dict(newton=4), dict(newton_variant=1), dict(serial_err=1), dict(thermal_sweep=1),
-                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1), dict(rank_jump=1), dict(quad=1), dict(wh_full_sweep=1), dict(rank_launches=1)])
+                                  dict(lakes_serial=1), dict(bps_up=1, bps_down=1, poll_sleep_ns=50), dict(level_order=1), dict(rank_jump=1), dict(quad=1), dict(wh_full_sweep=1), dict(rank_launches=1), dict(no_walk_cache=1)])
 def test_alternative_code_paths_match(knob):
     """The up-sweep solves a node with explicit in-range sqrt/division sequences and re-solves it with the
     plain operators if a range test ever failed: newton=4 forces the second solve for every node,
@@ -99,7 +99,8 @@ def test_alternative_code_paths_match(knob):
     grows the lake forest with the one-warp heap (the path degenerate inputs take) instead of the parallel
     fixed-point formulation; bps_*/poll_sleep_ns change the sweeps' occupancy and poll pacing; quad=1 runs the
     sediment sweep with four nodes per warp over the level order padded to quads (the default from 2048^2 on);
-    rank_launches=1 runs every pointer-jumping round as a launch of its own instead of one cooperative launch;
+    no_walk_cache=1 makes the stack build walk the parent forest for every pair of donors it cannot decide by their keys
+    (by default pairs that hang below the same two block anchors share one walk); rank_launches=1 runs every pointer-jumping round as a launch of its own instead of one cooperative launch;
     wh_full_sweep=1 walks every cell in the water-surface sweep instead of only those a running maximum leaves open."""
     for kind in (0, 1):
         f = synth.generate(7, 7, kind=kind)

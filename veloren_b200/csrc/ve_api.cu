@@ -220,7 +220,7 @@ int ve_create(ve_ctx** out, uint32_t x_lg, uint32_t y_lg, const int* device_ids,
     // selects the thread-per-node kernels instead (kept for comparison and covered by a test).
     ctx->lanes_down = ctx->lanes_up = ctx->lanes_other = 1u;
     ctx->dbg_df_bps = 0; ctx->dbg_newton = 0; ctx->dbg_lwv_small_log = 0; ctx->dbg_thermal_sweep = 0; ctx->dbg_lakes_trace = 0;
-    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->order_q = nullptr; ctx->order_q_n = nullptr; ctx->order_q_cap = 0; ctx->dbg_quad = 0; ctx->dbg_rank_jump = 0; ctx->dbg_rank_launches = 0; ctx->dbg_wh_full_sweep = 0; ctx->n_wh_undecided = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
+    ctx->dbg_lakes_serial = 0; ctx->lake_rounds = 0; ctx->order_q = nullptr; ctx->order_q_n = nullptr; ctx->order_q_cap = 0; ctx->dbg_quad = 0; ctx->dbg_rank_jump = 0; ctx->dbg_no_walk_cache = 0; ctx->dbg_rank_launches = 0; ctx->dbg_wh_full_sweep = 0; ctx->n_wh_undecided = 0; ctx->dbg_level_order = 0; ctx->bps_up = 0; ctx->bps_down = 0;
     ctx->mg_rank = 0; ctx->mg_world = 1; ctx->mg_shift = 31u; ctx->mg_cb = nullptr; ctx->mg_user = nullptr;
     ctx->mg_uw_flag = nullptr; ctx->mg_uw_val = nullptr; ctx->mg_errsq = nullptr; ctx->mg_order_own = nullptr;
     ctx->dbg_newton_variant = 0; ctx->dbg_serial_err = 0; ctx->dbg_poll_sleep_ns = 0; ctx->spin_limit_ns = 0;
@@ -298,6 +298,7 @@ int ve_set_debug(ve_ctx* ctx, const char* key, long long value) {
     else if (k == "quad") ctx->dbg_quad = (int)value;
     else if (k == "rank_jump") ctx->dbg_rank_jump = (int)value;
     else if (k == "level_order") ctx->dbg_level_order = (int)value;
+    else if (k == "no_walk_cache") ctx->dbg_no_walk_cache = (int)value;
     else if (k == "rank_launches") ctx->dbg_rank_launches = (int)value;
     else if (k == "wh_full_sweep") ctx->dbg_wh_full_sweep = (int)value;
     else if (k == "bps_up") ctx->bps_up = (int)value;

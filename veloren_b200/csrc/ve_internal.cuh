@@ -94,6 +94,7 @@ struct ve_ctx {
     int dbg_wh_full_sweep;    // 1: the water-surface sweep walks every cell (no pointer-jumping pre-pass)
     uint32_t n_wh_undecided;  // cells the last water-surface sweep had to walk
     int dbg_rank_launches;    // 1: one kernel launch per pointer-jumping round (else one cooperative launch for all rounds)
+    int dbg_no_walk_cache;    // 1: the parent sweep never reuses the answer of a pointer walk
     int dbg_rank_jump;        // 1: list ranking always by pointer jumping over all arcs
     uint32_t *order_q;        // level order padded to quads (four nodes per warp in the down-sweep) + level tables
     uint32_t order_q_cap; uint32_t *order_q_n;   // capacity in entries; padded length on the device (0: unusable)
