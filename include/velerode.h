@@ -119,7 +119,7 @@ int ve_mg_attach(ve_ctx* ctx, int rank, int world, ve_allgather_cb cb, void* use
  * "bps_up" / "bps_down" (resident blocks per SM of the two Gauss-Seidel sweeps), "level_order", "rank_jump",
  * "rank_launches" (one launch per pointer-jumping round instead of one cooperative launch), "quad" (four nodes per
  * warp in the sediment sweep: 1 always, -1 never, 0 from 2048x2048 cells on), "wh_full_sweep" (the water-surface
- * sweep walks every cell). */
+ * sweep walks every cell), "no_walk_cache" (the stack build never reuses the answer of a pointer walk). */
 int ve_set_debug(ve_ctx* ctx, const char* key, long long value);
 int ve_set_params(ve_ctx* ctx, const ve_params* p);
 int ve_set_noise(ve_ctx* ctx, const ve_noise_fbm_perlin3* nz);
